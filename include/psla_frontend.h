@@ -1,0 +1,104 @@
+/* psla_frontend.h -- C ABI of the B200-native PSLA feature frontend (libpsla_frontend.so).
+ *
+ * The reference (haoheliu/psla) has no FFI / plugin registry: its boundary for this path is the
+ * Python Dataset protocol, `AudiosetDataset.__getitem__` (src/dataloaders/audioset_dataset.py:139-202),
+ * which runs everything below on CPU dataloader workers.  Each entry point here replaces a piece of
+ * that method for a whole BATCH of clips on one GPU; the reference-side binding is the ctypes stub in
+ * INTEGRATION.md (and psla_b200/_lib.py is the one this repo ships).
+ *
+ * Conventions
+ *   - plain C types only; `stream` is a CUstream / cudaStream_t passed as void*.
+ *   - "device" pointers must be valid on the handle's device; the caller owns every buffer.
+ *   - forward() is asynchronous on `stream`.  Metadata arrays (offsets, indices, lambda, masks) are HOST
+ *     arrays: they are validated synchronously (so errors surface like the reference's Python exceptions)
+ *     and staged to the device by the library.
+ *   - every function returns PSLA_OK (0) or a negative psla_status; nothing is written to `out` on error.
+ *   - a handle may be used from one thread at a time; use one handle per stream for pipelining.
+ */
+#ifndef PSLA_FRONTEND_H_
+#define PSLA_FRONTEND_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct psla_frontend psla_frontend_t;
+
+typedef enum psla_status {
+    PSLA_OK = 0,
+    PSLA_E_INVALID = -1,      /* null pointer, negative size, index out of range, misaligned buffer */
+    PSLA_E_UNSUPPORTED = -2,  /* geometry other than 400/160/512 (16 kHz, 25 ms / 10 ms) or > 128 mel bins */
+    PSLA_E_SHORT_CLIP = -3,   /* a primary waveform has fewer samples than one frame; the reference raises
+                                 AssertionError at torchaudio/compliance/kaldi.py:142 */
+    PSLA_E_MASK = -4,         /* mask offsets outside [0, num_mel_bins] x [0, target_length] */
+    PSLA_E_WORKSPACE = -5,    /* workspace too small / misaligned */
+    PSLA_E_CUDA = -6,         /* a CUDA runtime call failed; psla_last_cuda_error() has the code */
+    PSLA_E_NOMEM = -7
+} psla_status;
+
+/* Replaces: the constants of the `kaldi.fbank(...)` call at audioset_dataset.py:119-120 plus the tables that
+ * call rebuilds every time (torchaudio/compliance/kaldi.py:94-95 Hann window, :436-511 get_mel_banks).
+ * high_freq <= 0 means "offset from Nyquist" exactly like kaldi.py:457-458. */
+int psla_frontend_create(psla_frontend_t** handle, int device, int sample_rate, int num_mel_bins,
+                         float frame_length_ms, float frame_shift_ms, float preemph, float low_freq,
+                         float high_freq);
+void psla_frontend_destroy(psla_frontend_t* handle);
+
+/* Optional: replace the natively built tables (host pointers).  `window` is [frame_length] = the analysis
+ * window itself (NOT pre-halved); `mel` is the dense [num_mel_bins][nfft/2] weight matrix.  Either may be
+ * NULL.  The Python host uses this to install tables built with torch ops in torchaudio's op order. */
+int psla_frontend_set_tables(psla_frontend_t* handle, const float* window, const float* mel);
+/* Read the tables back (host pointers, same shapes; either may be NULL). */
+int psla_frontend_get_tables(const psla_frontend_t* handle, float* window, float* mel);
+
+/* Bytes of device scratch forward() needs for a batch of `n_clips` (256-byte aligned pointer required). */
+size_t psla_frontend_workspace_bytes(const psla_frontend_t* handle, int n_clips);
+
+/* Replaces: AudiosetDataset._wav2fbank + the SpecAugment / normalisation tail of __getitem__
+ * (audioset_dataset.py:88-137, :177-192) for B clips.
+ *
+ *   wav         DEVICE  packed fp32 waveforms in [-1, 1] (what torchaudio.load returns, channel 0), 16-byte aligned
+ *   wav_offset  HOST    [n_wav] start sample of every waveform inside `wav` (a multiple of 4 enables 128-bit loads)
+ *   wav_length  HOST    [n_wav] number of samples of every waveform
+ *   src1        HOST    [B] primary waveform index of each output clip
+ *   src2        HOST    [B] mixup partner waveform index, or -1 (no mixup)                       (:147-156)
+ *   lambda      HOST    [B] float64 mixup lambda (np.random.beta draw, :114); ignored where src2 < 0
+ *   mask        HOST    [B][4] = f_start, f_width, t_start, t_width, drawn on the host exactly like
+ *                       torchaudio/functional/functional.py:939-943; width 0 = no mask; may be NULL   (:177-188)
+ *   norm_mean, norm_div  fbank = (fbank - norm_mean) / norm_div unless skip_norm                 (:191-192)
+ *   out         DEVICE  [B][target_length][num_mel_bins] fp32, 16-byte aligned
+ */
+int psla_frontend_forward(psla_frontend_t* handle, const float* wav, const int64_t* wav_offset, const int64_t* wav_length, int n_wav,
+                          const int32_t* src1, const int32_t* src2, const double* lambda, const int32_t* mask,
+                          int n_clips, int target_length, float norm_mean, float norm_div, int skip_norm,
+                          float* out, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Same, with HOST waveform and output buffers (pinned memory makes the copies asynchronous).  The library
+ * owns the device staging buffers (grown on demand, kept in the handle).  `out_host` may be NULL to leave the
+ * features on the device; psla_frontend_device_out() then returns the device pointer (valid until the next
+ * forward_host call on the same handle).  Asynchronous on `stream`. */
+int psla_frontend_forward_host(psla_frontend_t* handle, const float* wav_host, const int64_t* wav_offset, const int64_t* wav_length,
+                               int n_wav,
+                               const int32_t* src1, const int32_t* src2, const double* lambda, const int32_t* mask,
+                               int n_clips, int target_length, float norm_mean, float norm_div, int skip_norm,
+                               float* out_host, void* stream);
+float* psla_frontend_device_out(const psla_frontend_t* handle);
+
+/* Number of frames kaldi.fbank produces for n_samples (snip_edges=True, kaldi.py:63-67); < 0 if too short. */
+int psla_frontend_num_frames(const psla_frontend_t* handle, int64_t n_samples);
+/* Kernels launched by this handle since creation (bench.py reports it as gpu_launches). */
+int64_t psla_frontend_launch_count(const psla_frontend_t* handle);
+/* Select the log implementation: 0 = logf (default), 1 = lg2.approx based (abs err < 4e-6 on log-mel). */
+int psla_frontend_set_fast_log(psla_frontend_t* handle, int enable);
+
+const char* psla_strerror(int status);
+int psla_last_cuda_error(const psla_frontend_t* handle);
+const char* psla_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PSLA_FRONTEND_H_ */

@@ -1,0 +1,85 @@
+"""ctypes binding of include/psla_frontend.h (the C ABI of libpsla_frontend.so).
+
+There is deliberately no fallback: if the shared library is missing or cannot be loaded the import
+of the product path fails with an error that says how to build it.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import POINTER, c_char_p, c_double, c_float, c_int, c_int32, c_int64, c_size_t, c_void_p
+
+from .build import LIB
+
+PSLA_OK = 0
+STATUS_NAMES = {0: "PSLA_OK", -1: "PSLA_E_INVALID", -2: "PSLA_E_UNSUPPORTED", -3: "PSLA_E_SHORT_CLIP",
+                -4: "PSLA_E_MASK", -5: "PSLA_E_WORKSPACE", -6: "PSLA_E_CUDA", -7: "PSLA_E_NOMEM"}
+
+# every symbol include/psla_frontend.h declares: name -> (restype, argtypes)
+SYMBOLS = {
+    "psla_frontend_create": (c_int, [POINTER(c_void_p), c_int, c_int, c_int, c_float, c_float, c_float, c_float, c_float]),
+    "psla_frontend_destroy": (None, [c_void_p]),
+    "psla_frontend_set_tables": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "psla_frontend_get_tables": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "psla_frontend_workspace_bytes": (c_size_t, [c_void_p, c_int]),
+    "psla_frontend_forward": (c_int, [c_void_p, c_void_p, POINTER(c_int64), POINTER(c_int64), c_int, POINTER(c_int32), POINTER(c_int32),
+                                      POINTER(c_double), POINTER(c_int32), c_int, c_int, c_float, c_float, c_int,
+                                      c_void_p, c_void_p, c_size_t, c_void_p]),
+    "psla_frontend_forward_host": (c_int, [c_void_p, c_void_p, POINTER(c_int64), POINTER(c_int64), c_int, POINTER(c_int32), POINTER(c_int32),
+                                           POINTER(c_double), POINTER(c_int32), c_int, c_int, c_float, c_float, c_int,
+                                           c_void_p, c_void_p]),
+    "psla_frontend_device_out": (c_void_p, [c_void_p]),
+    "psla_frontend_num_frames": (c_int, [c_void_p, c_int64]),
+    "psla_frontend_launch_count": (c_int64, [c_void_p]),
+    "psla_frontend_set_fast_log": (c_int, [c_void_p, c_int]),
+    "psla_strerror": (c_char_p, [c_int]),
+    "psla_last_cuda_error": (c_int, [c_void_p]),
+    "psla_version": (c_char_p, []),
+}
+
+_lib = None
+
+
+class PslaError(RuntimeError):
+    def __init__(self, status: int, where: str, cuda: int = 0):
+        self.status = status
+        msg = f"{where}: {STATUS_NAMES.get(status, status)} ({strerror(status)})"
+        if cuda:
+            msg += f" [cudaError {cuda}]"
+        super().__init__(msg)
+
+
+class ShortClipError(PslaError, AssertionError):
+    """The reference raises AssertionError (torchaudio kaldi.py:142) for clips shorter than one frame."""
+
+
+def load() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB):
+            raise ImportError(
+                f"{LIB} is missing: the CUDA frontend has not been built (python -m psla_b200.build, or "
+                "__graft_entry__.build()).  psla_b200 has no CPU fallback.")
+        lib = ctypes.CDLL(LIB)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(lib, name)  # AttributeError if the .so does not export a declared symbol
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def strerror(status: int) -> str:
+    try:
+        return load().psla_strerror(int(status)).decode()
+    except Exception:
+        return "?"
+
+
+def check(status: int, where: str, handle=None):
+    if status == PSLA_OK:
+        return
+    cuda = load().psla_last_cuda_error(handle) if handle else 0
+    if status == -3:
+        raise ShortClipError(status, where, cuda)
+    raise PslaError(status, where, cuda)

@@ -1,0 +1,230 @@
+"""Batch-level GPU frontend: the host-side mirror of `AudiosetDataset._wav2fbank` + the SpecAugment /
+normalisation tail of `__getitem__` (src/dataloaders/audioset_dataset.py:88-137, 177-192), for a
+whole batch on one B200 through the C ABI in include/psla_frontend.h.
+
+    fe = GpuFbankFrontend(audio_conf)                 # same dict the reference's dataset takes
+    fbank = fe(waves, src1, src2, lam, masks)         # cuda FloatTensor [B, target_length, num_mel_bins]
+
+`fbank` is exactly the `[batch, time_frame_num, frequency_bins]` tensor `EffNetAttention.forward`
+expects (src/models/Models.py:104-107).  PyTorch is used only for device memory and streams.
+"""
+from __future__ import annotations
+
+import ctypes
+from dataclasses import dataclass
+from typing import Optional, Sequence, Union
+
+import numpy as np
+import torch
+
+from . import _lib, tables
+
+SAMPLE_RATE = 16000
+
+
+@dataclass
+class PackedWaves:
+    """Waveforms packed back to back in one fp32 buffer; every start is 16-byte aligned."""
+    wav: torch.Tensor  # 1-D float32 (cuda, or pinned / pageable host memory)
+    offsets: np.ndarray  # int64 [n_wav]; waveform i = wav[offsets[i] : offsets[i] + lengths[i]]
+    lengths: np.ndarray  # int64 [n_wav]
+
+    @property
+    def n_wav(self) -> int:
+        return len(self.lengths)
+
+
+def pack_waveforms(waves: Sequence[torch.Tensor], device: Union[str, torch.device, None] = None,
+                   pinned: bool = False) -> PackedWaves:
+    """Pack [1, n] / [n] fp32 waveforms (channel 0, as kaldi.fbank selects it, kaldi.py:136) with each start
+    rounded up to a multiple of 4 samples so the kernels can use 128-bit loads."""
+    lens = np.array([int(w.shape[-1]) for w in waves], dtype=np.int64)
+    starts = np.zeros(len(waves), dtype=np.int64)
+    pos = 0
+    for i, n in enumerate(lens):
+        starts[i] = pos
+        pos += (int(n) + 3) // 4 * 4
+    flat = torch.zeros(max(pos, 4), dtype=torch.float32, pin_memory=pinned)
+    for i, w in enumerate(waves):
+        w = w.detach()
+        w = w[0] if w.dim() == 2 else w
+        flat[starts[i]:starts[i] + lens[i]] = w.to(torch.float32)
+    if device is not None:
+        flat = flat.to(device, non_blocking=pinned)
+    return PackedWaves(flat, starts, lens)
+
+
+def _as_c(arr: Optional[np.ndarray], dtype, ctype):
+    if arr is None:
+        return None, None
+    a = np.ascontiguousarray(arr, dtype=dtype)
+    return a, a.ctypes.data_as(ctypes.POINTER(ctype))
+
+
+class GpuFbankFrontend:
+    """Kaldi-compatible log-mel + SpecAugment + normalisation on the GPU.
+
+    audio_conf keys (same as the reference, audioset_dataset.py:60-80,122): num_mel_bins, target_length,
+    mean, std, skip_norm (optional).  freqm / timem / mixup are consumed by the host-side parameter draw
+    (psla_b200.dataloaders), the kernel receives the drawn offsets.
+
+    norm_std_scale: 1.0 reproduces this reference (`/ norm_std`, :192); 2.0 gives the `/ (norm_std * 2)`
+    form of upstream PSLA/AST that BASELINE.json's north_star sentence quotes.
+    """
+
+    def __init__(self, audio_conf: dict, device: Union[int, str, torch.device, None] = None,
+                 norm_std_scale: float = 1.0, fast_log: bool = True, tables_from: str = "torch",
+                 sample_rate: int = SAMPLE_RATE):
+        if not torch.cuda.is_available():
+            raise RuntimeError("GpuFbankFrontend needs a CUDA device; psla_b200 has no CPU path")
+        self.lib = _lib.load()
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        if self.device.type != "cuda":
+            raise ValueError("device must be a CUDA device")
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        self.audio_conf = dict(audio_conf)
+        self.num_mel_bins = int(audio_conf.get("num_mel_bins"))
+        self.target_length = int(audio_conf.get("target_length"))
+        self.skip_norm = bool(audio_conf.get("skip_norm")) if audio_conf.get("skip_norm") else False
+        self.norm_mean = float(audio_conf.get("mean")) if audio_conf.get("mean") is not None else 0.0
+        std = audio_conf.get("std")
+        self.norm_std = float(std) if std is not None else 1.0
+        self.norm_std_scale = float(norm_std_scale)
+        # python-float arithmetic first, one rounding to fp32 when it meets the tensor (as torch does)
+        self.norm_div = self.norm_std * self.norm_std_scale
+        self.sample_rate = int(sample_rate)
+        h = ctypes.c_void_p()
+        st = self.lib.psla_frontend_create(ctypes.byref(h), self.device.index, self.sample_rate, self.num_mel_bins,
+                                           25.0, 10.0, 0.97, 20.0, 0.0)
+        _lib.check(st, "psla_frontend_create")
+        self._h = h
+        if tables_from == "torch":
+            win = tables.hann_window(400).numpy()
+            mel = tables.mel_banks(self.num_mel_bins, 512, float(self.sample_rate)).numpy()
+            st = self.lib.psla_frontend_set_tables(self._h, win.ctypes.data, np.ascontiguousarray(mel).ctypes.data)
+            _lib.check(st, "psla_frontend_set_tables", self._h)
+        elif tables_from != "native":
+            raise ValueError("tables_from must be 'torch' or 'native'")
+        self.set_fast_log(fast_log)
+        self._ws = {}
+
+    # ---- lifetime ----
+    def close(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            self.lib.psla_frontend_destroy(h)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- knobs / introspection ----
+    def set_fast_log(self, enable: bool):
+        self.fast_log = bool(enable)
+        _lib.check(self.lib.psla_frontend_set_fast_log(self._h, int(self.fast_log)), "set_fast_log", self._h)
+
+    @property
+    def launch_count(self) -> int:
+        return int(self.lib.psla_frontend_launch_count(self._h))
+
+    def num_frames(self, n_samples: int) -> int:
+        return int(self.lib.psla_frontend_num_frames(self._h, int(n_samples)))
+
+    def get_tables(self):
+        win = np.zeros(400, np.float32)
+        mel = np.zeros((self.num_mel_bins, 256), np.float32)
+        _lib.check(self.lib.psla_frontend_get_tables(self._h, win.ctypes.data, mel.ctypes.data), "get_tables")
+        return win, mel
+
+    def _workspace(self, n_clips: int) -> torch.Tensor:
+        need = int(self.lib.psla_frontend_workspace_bytes(self._h, n_clips))
+        ws = self._ws.get("buf")
+        if ws is None or ws.numel() < need:
+            ws = torch.empty(max(need, 1 << 16), dtype=torch.uint8, device=self.device)
+            self._ws["buf"] = ws
+        return ws
+
+    # ---- the hot path ----
+    def forward_packed(self, packed: PackedWaves, src1, src2=None, lam=None, masks=None,
+                       out: Optional[torch.Tensor] = None, target_length: Optional[int] = None) -> torch.Tensor:
+        """Device-resident waveforms -> [B, T, F] on the current CUDA stream (asynchronous)."""
+        T = self.target_length if target_length is None else int(target_length)
+        wav = packed.wav
+        if not wav.is_cuda:
+            raise ValueError("forward_packed needs device-resident waveforms; use forward_host for host buffers")
+        B = len(src1)
+        if out is None:
+            out = torch.empty((B, T, self.num_mel_bins), dtype=torch.float32, device=self.device)
+        elif tuple(out.shape) != (B, T, self.num_mel_bins) or out.dtype != torch.float32 or not out.is_contiguous():
+            raise ValueError("out must be a contiguous float32 [B, T, F] cuda tensor")
+        if B == 0:
+            return out
+        ao, p_off = _as_c(packed.offsets, np.int64, ctypes.c_int64)
+        an, p_len = _as_c(packed.lengths, np.int64, ctypes.c_int64)
+        a1, p1 = _as_c(np.asarray(src1), np.int32, ctypes.c_int32)
+        a2, p2 = _as_c(None if src2 is None else np.asarray(src2), np.int32, ctypes.c_int32)
+        al, pl = _as_c(None if lam is None else np.asarray(lam), np.float64, ctypes.c_double)
+        am, pm = _as_c(None if masks is None else np.asarray(masks).reshape(B, 4), np.int32, ctypes.c_int32)
+        ws = self._workspace(B)
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        st = self.lib.psla_frontend_forward(
+            self._h, wav.data_ptr(), p_off, p_len, packed.n_wav, p1, p2, pl, pm, B, T,
+            self.norm_mean, self.norm_div, int(self.skip_norm), out.data_ptr(), ws.data_ptr(), ws.numel(), stream)
+        _lib.check(st, "psla_frontend_forward", self._h)
+        return out
+
+    def forward_host(self, packed: PackedWaves, src1, src2=None, lam=None, masks=None,
+                     out_host: Optional[torch.Tensor] = None, target_length: Optional[int] = None,
+                     stream: Optional[torch.cuda.Stream] = None) -> Optional[torch.Tensor]:
+        """Host waveforms (ideally pinned) -> features through the host-buffer C entry point.  With `out_host`
+        (a pinned float32 [B, T, F] tensor) the result is copied back; without it a cuda tensor view of the
+        library-owned output buffer is returned (valid until the next forward_host on this frontend)."""
+        T = self.target_length if target_length is None else int(target_length)
+        wav = packed.wav
+        if wav.is_cuda:
+            raise ValueError("forward_host takes host waveforms")
+        B = len(src1)
+        ao, p_off = _as_c(packed.offsets, np.int64, ctypes.c_int64)
+        an, p_len = _as_c(packed.lengths, np.int64, ctypes.c_int64)
+        a1, p1 = _as_c(np.asarray(src1), np.int32, ctypes.c_int32)
+        a2, p2 = _as_c(None if src2 is None else np.asarray(src2), np.int32, ctypes.c_int32)
+        al, pl = _as_c(None if lam is None else np.asarray(lam), np.float64, ctypes.c_double)
+        am, pm = _as_c(None if masks is None else np.asarray(masks).reshape(B, 4), np.int32, ctypes.c_int32)
+        s = (stream or torch.cuda.current_stream(self.device)).cuda_stream
+        out_ptr = None
+        if out_host is not None:
+            if tuple(out_host.shape) != (B, T, self.num_mel_bins) or out_host.dtype != torch.float32 or out_host.is_cuda:
+                raise ValueError("out_host must be a host float32 [B, T, F] tensor")
+            out_ptr = out_host.data_ptr()
+        st = self.lib.psla_frontend_forward_host(
+            self._h, wav.data_ptr(), p_off, p_len, packed.n_wav, p1, p2, pl, pm, B, T,
+            self.norm_mean, self.norm_div, int(self.skip_norm), out_ptr, s)
+        _lib.check(st, "psla_frontend_forward_host", self._h)
+        if out_host is not None:
+            return out_host
+        return _DeviceView(self.lib.psla_frontend_device_out(self._h), (B, T, self.num_mel_bins), self.device).tensor()
+
+    def __call__(self, waves, src1=None, src2=None, lam=None, masks=None, **kw) -> torch.Tensor:
+        """waves: PackedWaves or a sequence of [1, n] / [n] tensors.  src1 defaults to one clip per waveform."""
+        if not isinstance(waves, PackedWaves):
+            waves = pack_waveforms(waves, device=self.device)
+        elif not waves.wav.is_cuda:
+            waves = PackedWaves(waves.wav.to(self.device, non_blocking=True), waves.offsets, waves.lengths)
+        if src1 is None:
+            src1 = np.arange(waves.n_wav, dtype=np.int32)
+        return self.forward_packed(waves, src1, src2, lam, masks, **kw)
+
+
+class _DeviceView:
+    """Zero-copy torch view of a library-owned device buffer (via __cuda_array_interface__)."""
+
+    def __init__(self, ptr: int, shape, device):
+        self._device = device
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f4", "data": (int(ptr), False),
+                                         "version": 3, "strides": None}
+
+    def tensor(self) -> torch.Tensor:
+        return torch.as_tensor(self, device=self._device)

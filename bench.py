@@ -1,0 +1,304 @@
+#!/usr/bin/env python
+"""bench.py -- clips/sec of the PSLA feature frontend on N B200s (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+One "step" = one AudioSet training batch (BASELINE.json configs[1]) through the hot path: 100 clips of 10 s @
+16 kHz, 150 waveforms, mixup on every even clip (rate 0.5), SpecAugment freqm=48 / timem=192, normalisation
+(mean -4.6476, std 4.5699) -> [100, 1056, 128] fp32.  Each rank owns a disjoint batch (weak scaling, no collective
+on the path); `value` = clips all ranks produced / max-over-ranks device time.
+
+JSON keys follow the driver's contract; see DESIGN.md "Measurement" for how roofline / e2e / cpu_baseline are taken.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "clips/sec (10 s 16 kHz -> 1056x128 log-mel)"
+UNIT = "clips/s"
+B_CLIPS, N_WAV, N_SAMPLES, T_FRAMES, N_MEL = 100, 150, 160000, 1056, 128
+N_SETS = 4  # distinct input sets / output buffers rotated between steps (working set > L2)
+NORM_MEAN, NORM_STD = -4.6476, 4.5699
+WORKLOAD = ("AudioSet training batch: 100 clips x 10 s @16 kHz (150 waveforms), mixup 0.5 (every even clip), "
+            "SpecAugment freqm=48 timem=192, norm mean=-4.6476 std=4.5699 (divisor = std, as in the reference), "
+            "target_length=1056, 128 mel bins")
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=300)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="bounded CPU-baseline sample (main arm, N=1)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def config_dict(n_gpus):
+    return {"workload": WORKLOAD, "clips_per_step_per_gpu": B_CLIPS, "sample_rate": 16000, "clip_seconds": 10,
+            "target_length": T_FRAMES, "num_mel_bins": N_MEL, "norm_divisor": "std (x1)", "parallelism": f"dp{n_gpus}",
+            "l2": f"inputs rotate over {N_SETS} distinct waveform sets ({N_SETS}x96 MB) and {N_SETS} output buffers "
+                  f"({N_SETS}x54 MB): working set 600 MB > 126 MB L2"}
+
+
+# ------------------------------------------------------------------------------------------------------
+# reference arm: the reference's CPU dataloader path (oracle port), all host cores
+# ------------------------------------------------------------------------------------------------------
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    from oracle import cpu_baseline  # the one other place bench.py may execute oracle/
+
+    r = cpu_baseline.time_steps(args.steps, args.warmup, batch=B_CLIPS)
+    line = {"impl": "reference", "metric": METRIC, "value": r["clips_per_s"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": r["steps"], "warmup": max(3, args.warmup), "ms_per_step": r["ms_per_step"], "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config_dict(args.gpus),
+            "cpu_baseline": {"value": r["clips_per_s"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]},
+            "e2e": {"value": r["clips_per_s"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------------
+# clocks sampled with NVML during the run
+# ------------------------------------------------------------------------------------------------------
+class ClockSampler(threading.Thread):
+    REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+               0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.samples, self.stop_flag, self.ok = [], False, False
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:  # pragma: no cover
+            self.err = repr(e)
+
+    def run(self):
+        if not self.ok:
+            return
+        while not self.stop_flag:
+            try:
+                mhz = self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)
+                rs = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h) if hasattr(
+                    self.nv, "nvmlDeviceGetCurrentClocksEventReasons") else self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                util = self.nv.nvmlDeviceGetUtilizationRates(self.h).gpu
+                self.samples.append((time.perf_counter(), mhz, rs, util))
+            except Exception:
+                pass
+            time.sleep(0.005)
+
+    def summary(self, t0, t1):
+        if not self.ok:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "note": "nvml unavailable: " + getattr(self, "err", "")}
+        win = [s for s in self.samples if t0 <= s[0] <= t1]
+        note = "sampled inside the timed region"
+        if len(win) < 3:
+            win = [s for s in self.samples if s[0] >= t0 - 0.5]
+            note = "timed region shorter than the sampling period; samples from the surrounding loaded interval"
+        if not win:
+            win = self.samples
+        bits = 0
+        for s in win:
+            bits |= s[2]
+        reasons = [n for b, n in self.REASONS.items() if bits & b and n != "gpu_idle"]
+        return {"sm_mhz": statistics.median(s[1] for s in win) if win else None, "sm_max_mhz": self.max_mhz,
+                "reasons": reasons, "samples": len(win), "note": note}
+
+
+# ------------------------------------------------------------------------------------------------------
+# main arm
+# ------------------------------------------------------------------------------------------------------
+def hbm_peak():
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(peaks["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, copy read+write)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s; MEASURED_PEAKS.json absent)"
+
+
+def ncu_traffic():
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "ncu_summary.json")))["fbank_tile_kernel"]["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
+def run_b200(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from psla_b200 import params as P
+    from psla_b200.frontend import GpuFbankFrontend, PackedWaves
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl b200 needs a CUDA device (there is no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    sampler = ClockSampler(local)
+    sampler.start()
+
+    # ---- synthetic inputs (per-rank seeds: disjoint batch slices) ----
+    conf = {"num_mel_bins": N_MEL, "target_length": T_FRAMES, "mean": NORM_MEAN, "std": NORM_STD}
+    gen = torch.Generator(device=dev).manual_seed(1234 + rank)
+    offsets = (np.arange(N_WAV, dtype=np.int64) * N_SAMPLES)
+    lengths = np.full(N_WAV, N_SAMPLES, dtype=np.int64)
+    sets = [PackedWaves(0.1 * torch.randn(N_WAV * N_SAMPLES, device=dev, generator=gen), offsets, lengths) for _ in range(N_SETS)]
+    outs = [torch.empty(B_CLIPS, T_FRAMES, N_MEL, device=dev) for _ in range(N_SETS)]
+    b = np.arange(B_CLIPS)
+    src1 = b.astype(np.int32)
+    src2 = np.where(b % 2 == 0, B_CLIPS + b // 2, -1).astype(np.int32)
+    lam = np.where(b % 2 == 0, np.random.default_rng(rank).beta(10, 10, B_CLIPS), 0.0)
+    torch.manual_seed(rank)
+    masks = np.array([P.draw_masks(48, 192, N_MEL, T_FRAMES) for _ in range(B_CLIPS)], dtype=np.int32)
+    alg_bytes = int(sum(4 * N_SAMPLES * (2 if s >= 0 else 1) + 4 * T_FRAMES * N_MEL for s in src2))
+
+    fe = GpuFbankFrontend(conf, device=dev)
+
+    def step(k):
+        fe.forward_packed(sets[k % N_SETS], src1, src2, lam, masks, out=outs[k % N_SETS])
+
+    # ---- value: device-resident inputs ----
+    for k in range(max(args.warmup, 3)):
+        step(k)
+    barrier()
+    l0 = fe.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_host0 = time.perf_counter()
+    e0.record()
+    for k in range(args.steps):
+        step(k)
+    e1.record()
+    barrier()
+    t_host1 = time.perf_counter()
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    launches = fe.launch_count - l0
+    value = world * B_CLIPS * args.steps / (ms * 1e-3)
+    checksum = float(outs[0][0, :4, :4].sum().item())
+
+    # ---- roofline: per-kernel device time of the same steps (events inside the library, same stream) ----
+    fe.set_timing(True)
+    torch.cuda.synchronize()
+    for k in range(args.steps):
+        step(k)
+    stats_ms, tile_ms, nfw = fe.get_timing()
+    fe.set_timing(False)
+    tile_avg_s = tile_ms / nfw * 1e-3
+    peak, peak_src = hbm_peak()
+    achieved = alg_bytes / tile_avg_s / 1e9
+    roofline = {"bound": "hbm", "kernel": "fbank_tile_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": ncu_traffic(), "algorithmic_bytes_per_launch": alg_bytes,
+                "kernel_ms": tile_ms / nfw, "stats_kernel_ms": stats_ms / nfw, "kernel_share_of_step": tile_ms / (tile_ms + stats_ms),
+                "peak_source": peak_src}
+
+    # ---- e2e: host (pinned) waveforms in, host (pinned) features out, through the host-buffer C entry point ----
+    n_pipe = 3
+    e2e_steps = max(3, min(args.steps, 60))
+    host_sets = [PackedWaves(s.wav.cpu().pin_memory(), offsets, lengths) for s in sets[:2]]
+    host_outs = [torch.empty(B_CLIPS, T_FRAMES, N_MEL, pin_memory=True) for _ in range(n_pipe)]
+    fes = [GpuFbankFrontend(conf, device=dev) for _ in range(n_pipe)]
+    streams = [torch.cuda.Stream(device=dev) for _ in range(n_pipe)]
+
+    def e2e_step(k):
+        j = k % n_pipe
+        fes[j].forward_host(host_sets[k % 2], src1, src2, lam, masks, out_host=host_outs[j], stream=streams[j])
+
+    for k in range(2 * n_pipe):
+        e2e_step(k)
+    barrier()
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    main = torch.cuda.current_stream(dev)
+    s0.record(main)
+    for s in streams:
+        s.wait_event(s0)
+    for k in range(e2e_steps):
+        e2e_step(k)
+    for s in streams:
+        main.wait_event(s.record_event())
+    s1.record(main)
+    barrier()
+    e2e_ms = max_over_ranks(s0.elapsed_time(s1))
+    e2e_value = world * B_CLIPS * e2e_steps / (e2e_ms * 1e-3)
+    e2e_launches = sum(f.launch_count for f in fes)
+    h2d = N_WAV * N_SAMPLES * 4 + B_CLIPS * 56
+    d2h = B_CLIPS * T_FRAMES * N_MEL * 4
+    e2e_ok = bool(torch.equal(host_outs[(e2e_steps - 1) % n_pipe], outs_check(fe, sets, (e2e_steps - 1) % 2, src1, src2, lam, masks)))
+
+    sampler.stop_flag = True
+    sampler.join(timeout=1.0)
+    clocks = sampler.summary(t_host0, t_host1)
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        from oracle import cpu_baseline  # timed CPU baseline leg only
+
+        r = cpu_baseline.time_budget(args.cpu_seconds, batch=B_CLIPS)
+        cpu = {"value": r["clips_per_s"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config_dict(world), "clocks": clocks,
+                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps, "pipeline_streams": n_pipe,
+                        "matches_device_path": e2e_ok, "gpu_launches": e2e_launches,
+                        "note": "pinned host waveforms -> psla_frontend_forward_host -> pinned host features; PCIe-bound"},
+                "gpu_launches": launches, "roofline": roofline, "checksum": checksum,
+                "hbm_roofline_frac_of_step": (alg_bytes * args.steps / (ms * 1e-3) / 1e9) / peak}
+        if cpu is not None:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def outs_check(fe, sets, idx, src1, src2, lam, masks):
+    import torch
+
+    o = fe.forward_packed(sets[idx], src1, src2, lam, masks)
+    torch.cuda.synchronize()
+    return o.cpu()
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    sys.exit(run_reference(a) if a.impl == "reference" else run_b200(a))

@@ -94,6 +94,12 @@ int64_t psla_frontend_launch_count(const psla_frontend_t* handle);
 /* Select the log implementation: 0 = logf (default), 1 = lg2.approx based (abs err < 4e-6 on log-mel). */
 int psla_frontend_set_fast_log(psla_frontend_t* handle, int enable);
 
+/* Per-kernel device timing for bench.py's roofline: while enabled, forward() brackets its two kernels with CUDA
+ * events on `stream`; get_timing() synchronises those events, returns the accumulated milliseconds of the
+ * clip-statistics kernel and of the fused tile kernel plus the number of forward() calls, and resets. */
+int psla_frontend_set_timing(psla_frontend_t* handle, int enable);
+int psla_frontend_get_timing(psla_frontend_t* handle, double* stats_ms, double* tile_ms, int64_t* n_forward);
+
 const char* psla_strerror(int status);
 int psla_last_cuda_error(const psla_frontend_t* handle);
 const char* psla_version(void);

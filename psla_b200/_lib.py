@@ -32,6 +32,8 @@ SYMBOLS = {
     "psla_frontend_num_frames": (c_int, [c_void_p, c_int64]),
     "psla_frontend_launch_count": (c_int64, [c_void_p]),
     "psla_frontend_set_fast_log": (c_int, [c_void_p, c_int]),
+    "psla_frontend_set_timing": (c_int, [c_void_p, c_int]),
+    "psla_frontend_get_timing": (c_int, [c_void_p, POINTER(c_double), POINTER(c_double), POINTER(c_int64)]),
     "psla_strerror": (c_char_p, [c_int]),
     "psla_last_cuda_error": (c_int, [c_void_p]),
     "psla_version": (c_char_p, []),

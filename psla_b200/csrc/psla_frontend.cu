@@ -21,329 +21,8 @@
 #include <vector>
 
 #include "../../include/psla_frontend.h"
-#include "fbank_tile.cuh"
+#include "frontend_kernels.cuh"
 #include "tables.h"
-
-namespace psla {
-
-// ------------------------------------------------------------------------------------------------
-// Device-side data
-// ------------------------------------------------------------------------------------------------
-struct ClipDesc {  // 56 bytes, one per output clip
-    long long off1, off2;  // start sample of the primary / partner waveform inside `wav`
-    int n1, n2;            // lengths; n2 == 0 means no mixup
-    float l1, l2;          // fp32(lambda), fp32(1 - lambda) (the latter rounded from the float64 difference)
-    int f0, f1;            // frequency mask [f0, f1)
-    int t0, t1;            // time mask [t0, t1)
-    int m_eff;             // min(num_frames(n1), target_length): rows that hold real features
-    int aligned;           // bit 0: off1 % 4 == 0, bit 1: off2 % 4 == 0 (float4 loads allowed)
-};
-static_assert(sizeof(ClipDesc) == 56, "ClipDesc layout");
-
-constexpr int kStatSegs = 8;  // partial sums per clip
-constexpr int kStatVals = 3;  // sum(w1), sum(w2), sum(w2[0:min(n1,n2)])
-
-// Flat constant-table buffer (floats), copied verbatim into shared memory by every CTA.
-constexpr int kTabWin = 0;                      // [416]  0.5 * window (400 used)
-constexpr int kTabTw = 416;                     // [1024] inter-pass twiddles (re, im)
-constexpr int kTabMelStart = kTabTw + 1024;     // 128 shorts
-constexpr int kTabMelCount = kTabMelStart + 64;  // 128 shorts
-constexpr int kTabSlotMax = kTabMelCount + 64;  // 4 ints
-constexpr int kTabSlotOff = kTabSlotMax + 4;    // 4 ints
-constexpr int kTabMelW = kTabSlotOff + 4;       // packed weights
-static_assert(kTabMelW % 4 == 0, "table buffer is copied as float4");
-
-// Shared-memory carve-up (floats)
-constexpr int kSmD = 0;
-constexpr int kSmXS = kSmD + kStageFloats;  // 48: XS[0..33], stats at [40..43]
-constexpr int kSmBS = kSmXS + 48;           // 352
-constexpr int kSmEX = kSmBS + 352;
-constexpr int kSmTab = kSmEX + kWarpsPerCta * 2 * kExPairFloats;
-static_assert((kSmEX * 4) % 16 == 0 && (kSmTab * 4) % 16 == 0, "16-byte alignment of vector regions");
-
-struct FbankParams {
-    const float* wav;
-    const ClipDesc* desc;
-    const double* partials;
-    const float* tab;
-    float* out;
-    int tab_floats;
-    int T;
-    int nmel;
-    float norm_mean, norm_div;
-    int skip_norm;
-    int fast_log;
-    float preemph, c1;
-};
-
-// 4 consecutive samples [i, i+4) of a waveform of n samples, zeros past the end
-__device__ __forceinline__ float4 load4(const float* __restrict__ w, int i, int n, bool aligned) {
-    if (aligned && i + 3 < n) return __ldg(reinterpret_cast<const float4*>(w + i));
-    float4 v;
-    v.x = (i < n) ? __ldg(w + i) : 0.f;
-    v.y = (i + 1 < n) ? __ldg(w + i + 1) : 0.f;
-    v.z = (i + 2 < n) ? __ldg(w + i + 2) : 0.f;
-    v.w = (i + 3 < n) ? __ldg(w + i + 3) : 0.f;
-    return v;
-}
-
-// ------------------------------------------------------------------------------------------------
-// Kernel 1: per-clip sums.  grid = (kStatSegs, B), block = 256.
-// ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) clip_stats_kernel(const float* __restrict__ wav, const ClipDesc* __restrict__ desc,
-                                                         double* __restrict__ partials) {
-    const int b = blockIdx.y, g = blockIdx.x, tid = threadIdx.x;
-    const ClipDesc d = desc[b];
-    float s1 = 0.f, s2 = 0.f, s2c = 0.f;
-    {
-        const int seg = ((d.n1 + 4 * kStatSegs - 1) / (4 * kStatSegs)) * 4;
-        const int lo = g * seg, hi = min(d.n1, lo + seg);
-        const float* w = wav + d.off1;
-        for (int i = lo + 4 * tid; i < hi; i += 4 * 256) {
-            const float4 v = load4(w, i, hi, d.aligned & 1);
-            s1 += (v.x + v.y) + (v.z + v.w);
-        }
-    }
-    if (d.n2 > 0) {
-        const int nmin = min(d.n1, d.n2);
-        const int seg = ((d.n2 + 4 * kStatSegs - 1) / (4 * kStatSegs)) * 4;
-        const int lo = g * seg, hi = min(d.n2, lo + seg);
-        const float* w = wav + d.off2;
-        for (int i = lo + 4 * tid; i < hi; i += 4 * 256) {
-            const float4 v = load4(w, i, hi, (d.aligned & 2) != 0);
-            s2 += (v.x + v.y) + (v.z + v.w);
-            if (i + 3 < nmin) {
-                s2c += (v.x + v.y) + (v.z + v.w);
-            } else {
-                s2c += (i < nmin ? v.x : 0.f) + (i + 1 < nmin ? v.y : 0.f) + (i + 2 < nmin ? v.z : 0.f);
-            }
-        }
-    }
-    __shared__ double red[8][kStatVals];
-    double v0 = s1, v1 = s2, v2 = s2c;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        v0 += __shfl_xor_sync(0xffffffffu, v0, o);
-        v1 += __shfl_xor_sync(0xffffffffu, v1, o);
-        v2 += __shfl_xor_sync(0xffffffffu, v2, o);
-    }
-    if ((tid & 31) == 0) {
-        red[tid >> 5][0] = v0;
-        red[tid >> 5][1] = v1;
-        red[tid >> 5][2] = v2;
-    }
-    __syncthreads();
-    if (tid < kStatVals) {
-        double s = 0.0;
-        for (int w = 0; w < 8; ++w) s += red[w][tid];
-        partials[(static_cast<size_t>(b) * kStatSegs + g) * kStatVals + tid] = s;
-    }
-}
-
-// ------------------------------------------------------------------------------------------------
-// Kernel 2: the fused tile kernel.  grid = (ceil(T / 32), B), block = 256, 2 CTAs / SM.
-// ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads, 2) fbank_tile_kernel(const FbankParams p) {
-    extern __shared__ __align__(16) float smem[];
-    float* D = smem + kSmD;
-    float* XS = smem + kSmXS;
-    float* BS = smem + kSmBS;
-    float* EX = smem + kSmEX;
-    float* TAB = smem + kSmTab;
-
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int b = blockIdx.y;
-    const int F0 = blockIdx.x * kFramesPerCta;
-    const ClipDesc d = p.desc[b];
-    const float fill = p.skip_norm ? 0.f : __fdiv_rn(__fsub_rn(0.f, p.norm_mean), p.norm_div);
-    float* out = p.out + static_cast<size_t>(b) * p.T * p.nmel;
-
-    // rows of this tile that carry computed features: inside the clip and outside the time mask
-    const int tile_hi = min(F0 + kFramesPerCta, d.m_eff);
-    const int masked = max(0, min(tile_hi, d.t1) - max(F0, d.t0));
-    const bool tile_live = (tile_hi - F0 - masked) > 0;
-
-    const int fw0 = F0 + kFramesPerWarp * warp;
-    unsigned live = 0;
-#pragma unroll
-    for (int q = 0; q < kFramesPerWarp; ++q) {
-        const int fa = fw0 + q;
-        if (fa < d.m_eff && !(fa >= d.t0 && fa < d.t1)) live |= 1u << q;
-    }
-
-    float acc[kMelSlots][kFramesPerWarp];
-#pragma unroll
-    for (int i = 0; i < kMelSlots; ++i)
-#pragma unroll
-        for (int q = 0; q < kFramesPerWarp; ++q) acc[i][q] = 0.f;
-
-    if (tile_live) {
-        // ---- constant tables -> shared memory; clip statistics ----
-        {
-            const float4* src = reinterpret_cast<const float4*>(p.tab);
-            float4* dst = reinterpret_cast<float4*>(TAB);
-            for (int i = tid; i < p.tab_floats / 4; i += kThreads) dst[i] = __ldg(src + i);
-        }
-        if (tid == 0) {
-            const double* ps = p.partials + static_cast<size_t>(b) * kStatSegs * kStatVals;
-            double s1 = 0.0, s2 = 0.0, s2c = 0.0;
-            for (int g = 0; g < kStatSegs; ++g) {
-                s1 += ps[g * kStatVals];
-                s2 += ps[g * kStatVals + 1];
-                s2c += ps[g * kStatVals + 2];
-            }
-            const float mean1 = static_cast<float>(s1 / d.n1);
-            float mean2 = 0.f, mixmean = 0.f;
-            if (d.n2 > 0) {
-                mean2 = static_cast<float>(s2 / d.n2);
-                const int nmin = min(d.n1, d.n2);
-                // mean over n1 samples of l1*(w1-mean1) + l2*(w2'-mean2), w2' zero-padded / cut to n1
-                const double r1 = s1 - static_cast<double>(d.n1) * mean1;
-                const double r2 = s2c - static_cast<double>(nmin) * mean2;
-                mixmean = static_cast<float>((static_cast<double>(d.l1) * r1 + static_cast<double>(d.l2) * r2) / d.n1);
-            }
-            XS[40] = mean1;
-            XS[41] = mean2;
-            XS[42] = mixmean;
-        }
-        __syncthreads();
-
-        // ---- stage samples: x = mixed & mean-removed waveform, D = x[j] - p*x[j-1] ----
-        const float mean1 = XS[40], mean2 = XS[41], mixmean = XS[42];
-        const bool mix = d.n2 > 0;
-        const int nmin = min(d.n1, d.n2);
-        const float* w1 = p.wav + d.off1;
-        const float* w2 = p.wav + d.off2;
-        const int S0 = F0 * kFrameShift;
-        const float pe = p.preemph, c1 = p.c1;
-        auto xval = [&](float a, float c, int s) -> float {  // audioset_dataset.py:92 / :98-117, same op order
-            if (s >= d.n1) return 0.f;
-            float v = __fsub_rn(a, mean1);
-            if (mix) {
-                const float v2 = (s < nmin) ? __fsub_rn(c, mean2) : 0.f;
-                v = __fsub_rn(__fadd_rn(__fmul_rn(d.l1, v), __fmul_rn(d.l2, v2)), mixmean);
-            }
-            return v;
-        };
-        constexpr int kGroups = kTileSamples / 4;  // 1340
-#pragma unroll 1
-        for (int it = 0; it < (kGroups + kThreads - 1) / kThreads; ++it) {
-            const int g = tid + it * kThreads;
-            const int u = 4 * g, s = S0 + u;
-            const bool in = g < kGroups;
-            float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (in) {
-                const float4 a = load4(w1, s, d.n1, d.aligned & 1);
-                float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (mix) c = load4(w2, s, nmin, (d.aligned & 2) != 0);
-                x.x = xval(a.x, c.x, s);
-                x.y = xval(a.y, c.y, s + 1);
-                x.z = xval(a.z, c.z, s + 2);
-                x.w = xval(a.w, c.w, s + 3);
-            }
-            float prev = __shfl_up_sync(0xffffffffu, x.w, 1);
-            if (lane == 0) {
-                prev = 0.f;
-                if (in && u > 0 && s - 1 < d.n1) {
-                    const float a = __ldg(w1 + s - 1);
-                    const float c = (mix && s - 1 < nmin) ? __ldg(w2 + s - 1) : 0.f;
-                    prev = xval(a, c, s - 1);
-                }
-            }
-            float s4 = (x.x + x.y) + (x.z + x.w);
-            s4 += __shfl_xor_sync(0xffffffffu, s4, 1);
-            s4 += __shfl_xor_sync(0xffffffffu, s4, 2);
-            if (in) {
-                float4 dd;
-                dd.x = fmaf(-pe, prev, x.x);
-                dd.y = fmaf(-pe, x.x, x.y);
-                dd.z = fmaf(-pe, x.y, x.z);
-                dd.w = fmaf(-pe, x.z, x.w);
-                *reinterpret_cast<float4*>(D + dpad(u)) = dd;
-                if ((lane & 3) == 0) BS[g >> 2] = s4;
-                if (u % kFrameShift == 0 && u / kFrameShift < kFramesPerCta) XS[u / kFrameShift] = c1 * x.x;
-            }
-        }
-        __syncthreads();
-
-        if (live) {
-            const float* WIN = TAB + kTabWin;
-            const float* TW = TAB + kTabTw;
-            MelTableView mt;
-            mt.start = reinterpret_cast<const short*>(TAB + kTabMelStart);
-            mt.count = reinterpret_cast<const short*>(TAB + kTabMelCount);
-            mt.slot_max = reinterpret_cast<const int*>(TAB + kTabSlotMax);
-            mt.slot_off = reinterpret_cast<const int*>(TAB + kTabSlotOff);
-            mt.w = TAB + kTabMelW;
-
-            // per-frame means (kaldi.py:183-186) from the 16-sample block sums; lanes 0..3 own one frame each
-            float cmu = 0.f;
-            if (lane < kFramesPerWarp) {
-                const float* bs = BS + 10 * (kFramesPerWarp * warp + lane);
-                float sum = 0.f;
-#pragma unroll
-                for (int k = 0; k < 25; ++k) sum += bs[k];
-                cmu = c1 * (sum * (1.0f / kFrameLen));
-            }
-            const int h = lane >> 4, n2 = lane & 15;
-            const float cmu_x = __shfl_sync(0xffffffffu, cmu, 2 * h);
-            const float cmu_y = __shfl_sync(0xffffffffu, cmu, 2 * h + 1);
-
-            float* EXw = EX + warp * 2 * kExPairFloats;
-            float* EXp = EXw + h * kExPairFloats;
-            pair_pass1(n2, kFramesPerWarp * warp + 2 * h, D, XS, WIN, TW, EXp, cmu_x, cmu_y);
-            __syncwarp();
-            {
-                float ar[16], ai[16], br[16], bi[16];
-                pair_pass2_fft(n2, EXp, ar, ai, br, bi);
-                __syncwarp();  // P aliases EX: all reads done before any write
-                pair_power_store(n2, ar, ai, br, bi, EXw + (2 * h) * kPRowFloats, EXw + (2 * h + 1) * kPRowFloats);
-            }
-            __syncwarp();
-            warp_mel(lane, EXw, mt, acc);
-        }
-    }
-
-    // ---- epilogue: log floor, SpecAugment fill, normalisation, coalesced streaming store ----
-    const float eps = 1.1920928955078125e-07f;   // kaldi.py:22
-    const float log_eps = -15.9423847198486328f;  // fp32 log(eps): what max(x, eps).log() gives on the floor
-    const float rdiv = __frcp_rn(p.norm_div);
-#pragma unroll
-    for (int i = 0; i < kMelSlots; ++i) {
-        const int j = lane + 32 * i;
-        if (j >= p.nmel) continue;
-        const bool fmasked = (j >= d.f0 && j < d.f1);
-#pragma unroll
-        for (int q = 0; q < kFramesPerWarp; ++q) {
-            const int row = fw0 + q;
-            if (row >= p.T) continue;
-            float v = fill;
-            if (((live >> q) & 1u) && !fmasked) {
-                const float e = acc[i][q];
-                float lg;
-                if (p.fast_log) {
-                    lg = (e > eps) ? __logf(e) : log_eps;
-                } else {
-                    lg = logf(fmaxf(e, eps));
-                }
-                if (p.skip_norm) {
-                    v = lg;
-                } else if (p.fast_log) {
-                    // (lg - mean) / div as one Newton-corrected multiply by 1/div (correctly rounded but for
-                    // rare last-bit cases; live cells only need 1e-3, the fill constant above is exact)
-                    const float x = __fsub_rn(lg, p.norm_mean);
-                    const float q0 = x * rdiv;
-                    v = fmaf(fmaf(-q0, p.norm_div, x), rdiv, q0);
-                } else {
-                    v = __fdiv_rn(__fsub_rn(lg, p.norm_mean), p.norm_div);
-                }
-            }
-            __stcs(out + static_cast<size_t>(row) * p.nmel + j, v);
-        }
-    }
-}
-
-}  // namespace psla
 
 // ================================================================================================
 // Host side: handle, tables, validation, launches (C ABI)
@@ -362,6 +41,11 @@ struct psla_frontend {
     int tab_floats = 0;
     size_t smem_bytes = 0;
     int fast_log = 0;
+    int timing = 0;
+    struct EvTriple {
+        cudaEvent_t e[3];
+    };
+    std::vector<EvTriple> timed;
     int64_t launches = 0;
     int last_cuda = 0;
     // pinned descriptor staging ring
@@ -507,6 +191,8 @@ void psla_frontend_destroy(psla_frontend_t* h) {
     if (!h) return;
     DeviceGuard guard(h->device);
     cudaDeviceSynchronize();
+    for (auto& t : h->timed)
+        for (auto& e : t.e) cudaEventDestroy(e);
     for (auto& s : h->slots) {
         if (s.host) cudaFreeHost(s.host);
         if (s.ev) cudaEventDestroy(s.ev);
@@ -554,6 +240,32 @@ int psla_frontend_num_frames(const psla_frontend_t* h, int64_t n_samples) {
 }
 
 int64_t psla_frontend_launch_count(const psla_frontend_t* h) { return h ? h->launches : 0; }
+
+int psla_frontend_set_timing(psla_frontend_t* h, int enable) {
+    if (!h) return PSLA_E_INVALID;
+    h->timing = enable ? 1 : 0;
+    return PSLA_OK;
+}
+
+int psla_frontend_get_timing(psla_frontend_t* h, double* stats_ms, double* tile_ms, int64_t* n_forward) {
+    if (!h) return PSLA_E_INVALID;
+    DeviceGuard guard(h->device);
+    double a = 0.0, b = 0.0;
+    for (auto& t : h->timed) {
+        float m0 = 0.f, m1 = 0.f;
+        PSLA_CUDA(h, cudaEventSynchronize(t.e[2]));
+        PSLA_CUDA(h, cudaEventElapsedTime(&m0, t.e[0], t.e[1]));
+        PSLA_CUDA(h, cudaEventElapsedTime(&m1, t.e[1], t.e[2]));
+        a += m0;
+        b += m1;
+        for (auto& e : t.e) cudaEventDestroy(e);
+    }
+    if (stats_ms) *stats_ms = a;
+    if (tile_ms) *tile_ms = b;
+    if (n_forward) *n_forward = static_cast<int64_t>(h->timed.size());
+    h->timed.clear();
+    return PSLA_OK;
+}
 
 int psla_frontend_set_fast_log(psla_frontend_t* h, int enable) {
     if (!h) return PSLA_E_INVALID;
@@ -625,6 +337,7 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
             return PSLA_E_INVALID;
         }
         d.aligned = ((d.off1 & 3) == 0 ? 1 : 0) | ((d.off2 & 3) == 0 ? 2 : 0);
+        d.pad0 = d.pad1 = 0;
         d.f0 = d.f1 = d.t0 = d.t1 = 0;
         if (mask) {
             const int32_t* m = mask + 4 * b;
@@ -652,8 +365,14 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
     slot.pending = true;
     h->next_slot = (h->next_slot + 1) % 4;
 
+    psla_frontend::EvTriple ev{};
+    if (h->timing) {
+        for (auto& e : ev.e) PSLA_CUDA(h, cudaEventCreate(&e));
+        PSLA_CUDA(h, cudaEventRecord(ev.e[0], stream));
+    }
     clip_stats_kernel<<<dim3(kStatSegs, n_clips), 256, 0, stream>>>(wav, d_desc, d_part);
     PSLA_CUDA(h, cudaGetLastError());
+    if (h->timing) PSLA_CUDA(h, cudaEventRecord(ev.e[1], stream));
 
     FbankParams p;
     p.wav = wav;
@@ -666,6 +385,12 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
     p.nmel = h->nmel;
     p.norm_mean = norm_mean;
     p.norm_div = norm_div;
+    p.norm_rdiv = 1.0f / norm_div;
+    // the value every masked / padded cell takes: (0 - mean) / std evaluated like torch does (fp32 sub, IEEE div)
+    {
+        volatile float z = 0.0f - norm_mean;
+        p.fill = skip_norm ? 0.0f : z / norm_div;
+    }
     p.skip_norm = skip_norm ? 1 : 0;
     p.fast_log = h->fast_log;
     p.preemph = h->preemph;
@@ -673,6 +398,10 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
     const int tiles = (target_length + kFramesPerCta - 1) / kFramesPerCta;
     fbank_tile_kernel<<<dim3(tiles, n_clips), kThreads, h->smem_bytes, stream>>>(p);
     PSLA_CUDA(h, cudaGetLastError());
+    if (h->timing) {
+        PSLA_CUDA(h, cudaEventRecord(ev.e[2], stream));
+        h->timed.push_back(ev);
+    }
     h->launches += 2;
     return PSLA_OK;
 }

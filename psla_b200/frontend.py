@@ -126,6 +126,16 @@ class GpuFbankFrontend:
         self.fast_log = bool(enable)
         _lib.check(self.lib.psla_frontend_set_fast_log(self._h, int(self.fast_log)), "set_fast_log", self._h)
 
+    def set_timing(self, enable: bool):
+        _lib.check(self.lib.psla_frontend_set_timing(self._h, int(bool(enable))), "set_timing", self._h)
+
+    def get_timing(self):
+        """(stats_kernel_ms, tile_kernel_ms, n_forward) accumulated since the last call; synchronises."""
+        a, b, n = ctypes.c_double(), ctypes.c_double(), ctypes.c_int64()
+        _lib.check(self.lib.psla_frontend_get_timing(self._h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(n)),
+                   "get_timing", self._h)
+        return a.value, b.value, n.value
+
     @property
     def launch_count(self) -> int:
         return int(self.lib.psla_frontend_launch_count(self._h))

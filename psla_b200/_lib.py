@@ -32,6 +32,7 @@ SYMBOLS = {
     "psla_frontend_num_frames": (c_int, [c_void_p, c_int64]),
     "psla_frontend_launch_count": (c_int64, [c_void_p]),
     "psla_frontend_set_fast_log": (c_int, [c_void_p, c_int]),
+    "psla_frontend_set_exact_clip_mean": (c_int, [c_void_p, c_int]),
     "psla_frontend_set_timing": (c_int, [c_void_p, c_int]),
     "psla_frontend_get_timing": (c_int, [c_void_p, POINTER(c_double), POINTER(c_double), POINTER(c_int64)]),
     "psla_strerror": (c_char_p, [c_int]),

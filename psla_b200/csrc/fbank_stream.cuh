@@ -1,0 +1,336 @@
+// Per-lane phases of the warp-autonomous streaming fbank kernel (sm_100a), also compilable by g++ for the CPU
+// lane-stepping harness in tests/emu/ (see fft_core.cuh).
+//
+// Geometry (fixed: 16 kHz, 25 ms / 10 ms => 400-sample frames every 160 samples, 512-point FFT;
+// torchaudio/compliance/kaldi.py:138-140 as called at src/dataloaders/audioset_dataset.py:119-120).
+//
+// Work unit of a WARP: a GROUP of 4 consecutive frames of one clip = 880 staged samples.  A warp walks along a
+// clip group by group; the 240 samples two consecutive groups share stay in its private shared-memory window,
+// only 640 new samples are staged per step.  No CTA-level barrier exists after the table load.
+//
+// Inside a group each HALF-WARP turns a frame pair (x, y) into ONE 512-point complex FFT of z = x + i*y
+// (32 complex values = 64 registers per lane):
+//   pass 1   lane n2 (0..15) holds z[16*n1 + n2], n1 = 0..31 (only n1 < 25 is non-zero: 400 = 25*16).  The y frame
+//            starts 160 samples = 10 n1-steps after the x frame, so ONE run of 35 staged values feeds both.
+//            -> 32-point DIF FFT over n1 in registers (first stage pruned for the 7 zero inputs) -> shared memory
+//            EX[k1][n2], untwiddled (row 0 pre-multiplied by W_32^-n2, see below).
+//   pass 2   lane t reads rows ka = t and kb = 32 - t (lane 0: rows 0 and 16), multiplies row ka by
+//            TW[t][n2] = W_512^(t*n2) and row kb by conj(TW[t][n2]): because W_512^((32-t)*n2) = W_16^n2 * conj(TW[t][n2])
+//            and a modulation by W_16^n2 only rotates the 16-point FFT's output index by one, both rows share one
+//            table row.  Two 16-point DIF FFTs over n2 in registers.  Z[k] and Z[512-k] are then in the SAME lane, so
+//            the two real spectra separate without any exchange (the 1/2 is folded into the window table); the power
+//            spectra go to shared memory as P[bin][frame 0..3].
+//            Lane 0's table row is W_32^n2 (what row 16 needs after conj + rotation); pass 1 compensates row 0.
+//   mel      the whole warp: lane l owns 4 mel bins (one per slot); per tap ONE 128-bit load brings the bin's power of
+//            all 4 frames; sparse triangle weights as fp32 FMAs.
+#pragma once
+
+#include "fft_core.cuh"
+
+namespace psla {
+
+// 8- and 16-byte shared-memory accesses (plain scalar code on the host harness)
+PSLA_HD void st2(float* p, float a, float b) {
+#if defined(__CUDA_ARCH__)
+    *reinterpret_cast<float2*>(p) = make_float2(a, b);
+#else
+    p[0] = a;
+    p[1] = b;
+#endif
+}
+PSLA_HD void ld2(const float* p, float& a, float& b) {
+#if defined(__CUDA_ARCH__)
+    const float2 v = *reinterpret_cast<const float2*>(p);
+    a = v.x;
+    b = v.y;
+#else
+    a = p[0];
+    b = p[1];
+#endif
+}
+PSLA_HD void ld4(const float* p, float& a, float& b, float& c, float& d) {
+#if defined(__CUDA_ARCH__)
+    const float4 v = *reinterpret_cast<const float4*>(p);
+    a = v.x;
+    b = v.y;
+    c = v.z;
+    d = v.w;
+#else
+    a = p[0];
+    b = p[1];
+    c = p[2];
+    d = p[3];
+#endif
+}
+
+constexpr int kFrameLen = 400;
+constexpr int kFrameShift = 160;
+constexpr int kNfft = 512;
+constexpr int kNumBins = kNfft / 2 + 1;  // 257
+constexpr int kMaxMel = 128;
+
+constexpr int kGroupFrames = 4;                                                  // frames per warp step
+constexpr int kGroupSamples = (kGroupFrames - 1) * kFrameShift + kFrameLen;      // 880
+constexpr int kStepSamples = kGroupFrames * kFrameShift;                         // 640 new samples per step
+constexpr int kOverlapSamples = kGroupSamples - kStepSamples;                    // 240
+
+// Staged-sample layout of a warp's window: 16 floats of padding after every 320 samples so that the two half-warps
+// (whose frame pairs start 320 samples apart, i.e. on the same bank) read disjoint bank halves.
+PSLA_HDC int dpad(int u) { return u + 16 * (u / 320); }
+constexpr int kDFloats = 912;  // dpad(879) + 1
+constexpr int kBsFloats = 56;  // 55 sums of 16 samples
+constexpr int kXsFloats = 8;   // (1-p) * x at u = 0, 160, ..., 800
+// Exchange buffer of one frame pair: 32 rows (k1) x 16 complex (n2), row stride 36 floats so that pass-2 row reads
+// (LDS.128, one row per lane) are bank-conflict free.
+constexpr int kExRowFloats = 36;
+constexpr int kExPairFloats = 32 * kExRowFloats;  // 1152 floats = 4608 B
+// Power spectra of the warp's 4 frames, P[bin][frame], alias the exchange buffers once pass 2 has read them.
+constexpr int kPFloats = 4 * (kNfft / 2);  // bins 0..255 (bin 256 never carries mel weight: kaldi.py:627 pads a zero column)
+static_assert(kPFloats <= 2 * kExPairFloats, "P must fit in the warp's exchange buffers");
+
+// per-warp shared-memory window (floats)
+constexpr int kWsD = 0;
+constexpr int kWsBS = kWsD + kDFloats;
+constexpr int kWsXS = kWsBS + kBsFloats;
+constexpr int kWsCS = kWsXS + kXsFloats;  // per-clip state of the warp (kept out of the register file, see stream_kernel.cuh)
+constexpr int kCsWords = 24;
+constexpr int kWsEX = kWsCS + kCsWords;
+constexpr int kWarpFloats = kWsEX + 2 * kExPairFloats;  // 3304 floats = 13216 B
+static_assert((kWsEX * 4) % 16 == 0 && (kWarpFloats * 4) % 16 == 0, "16-byte alignment of vector regions");
+
+// Constant tables (floats), copied once per CTA into shared memory.
+constexpr int kWinRow = 28;                            // WINT[n2][n1], n1 < 25, zero padded: 0.5 * window[16*n1 + n2]
+constexpr int kTabWin = 0;                             // [16][28]
+constexpr int kTabTw = kTabWin + 16 * kWinRow;         // [16][36]: TW[t][n2] (re, im), row stride 36 floats
+constexpr int kTabTwz = kTabTw + 16 * kExRowFloats;    // [16] (re, im): W_32^(-n2), applied to row 0 in pass 1
+constexpr int kTabMelStart = kTabTwz + 32;             // [4][32] ints: first P bin of (slot, lane)
+constexpr int kTabMelBin = kTabMelStart + 128;         // [4][32] ints: mel bin owned by (slot, lane), -1 = none
+constexpr int kTabMelInfo = kTabMelBin + 128;          // [8] ints: slot_max[4], slot_off[4] (rows of W before the slot)
+constexpr int kTabMelW = kTabMelInfo + 8;              // [sum slot_max][32] weights
+static_assert(kTabTw % 4 == 0 && kTabTwz % 4 == 0 && kTabMelW % 4 == 0, "table regions are float4 aligned");
+
+constexpr int kMelSlots = 4;
+constexpr int kMelMaxCount = 128;  // per-row tap bound of the generic path (the table must also fit in shared memory)
+// tap counts the specialised (fully unrolled) mel path is compiled for: 16 kHz / 128 bins needs (2, 3, 6, 10)
+constexpr int kMelSpec0 = 2, kMelSpec1 = 3, kMelSpec2 = 6, kMelSpec3 = 10;
+
+// ---------------------------------------------------------------------------------------------
+// 32-point DIF FFT whose inputs n1 >= 25 are zero: the first stage pairs (j, j+16); for j >= 9 the upper input is
+// zero, so the butterfly degenerates to (u, u * W_32^j) -- no additions.
+// ---------------------------------------------------------------------------------------------
+PSLA_HD void fft32_zero_tail(float (&re)[32], float (&im)[32]) {
+    static_for<0, 16>([&](auto j_) {
+        constexpr int j = decltype(j_)::value;
+        if constexpr (j + 16 < 25) {
+            const float ur = re[j], ui = im[j], vr = re[j + 16], vi = im[j + 16];
+            re[j] = ur + vr;
+            im[j] = ui + vi;
+            float dr = ur - vr, di = ui - vi;
+            mul_twiddle<j, 32>(dr, di);
+            re[j + 16] = dr;
+            im[j + 16] = di;
+        } else {
+            float dr = re[j], di = im[j];
+            mul_twiddle<j, 32>(dr, di);
+            re[j + 16] = dr;
+            im[j + 16] = di;
+        }
+    });
+    fft_dif<32, 16>(re, im);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Pass 1 of half-warp h, lane n2: frames 2h (x) and 2h+1 (y) of the group.
+//   D     staged d[u] = x[u] - p*x[u-1] in dpad() layout,  XS[f] = (1-p) * x[160 f]
+//   cmu_* per-frame means pre-multiplied by (1-p): per-frame DC removal (kaldi.py:183-186) and pre-emphasis
+//         (:193-198) commute into  d[j] - (1-p)*mu  (first sample: (1-p)*(x0 - mu), replicate padding)
+// ---------------------------------------------------------------------------------------------
+PSLA_HD void pair_pass1(int n2, int h, const float* __restrict__ D, const float* __restrict__ XS,
+                        const float* __restrict__ WINT, const float* __restrict__ TWZ, float* __restrict__ EX,
+                        float cmu_x, float cmu_y) {
+    float re[32], im[32];
+    {
+        // element n1 of the run sits at dx[16*n1 + (n1 >= 20 ? 16 : 0)]; x frame: n1 = 0..24, y frame: n1 = 10..34
+        const float* dx = D + 336 * h + n2;
+        // replicate-padded first samples: lane 0 reads (1-p)*x0 from XS instead of d[0]; an address select, so that
+        // lane 0 does not get a code path of its own
+        const float* x0p = (n2 == 0) ? XS + 2 * h : dx;
+        const float* y0p = (n2 == 0) ? XS + 2 * h + 1 : dx + 160;
+        float w[kWinRow];
+        static_for<0, kWinRow / 4>([&](auto q_) {
+            constexpr int q = decltype(q_)::value;
+            ld4(WINT + kWinRow * n2 + 4 * q, w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+        });
+        float v[35];
+        static_for<0, 35>([&](auto n1_) {
+            constexpr int n1 = decltype(n1_)::value;
+            v[n1] = (n1 == 0) ? x0p[0] : dx[16 * n1 + (n1 >= 20 ? 16 : 0)];
+        });
+        const float vy0 = y0p[0];
+        static_for<0, 25>([&](auto n1_) {
+            constexpr int n1 = decltype(n1_)::value;
+            re[n1] = (v[n1] - cmu_x) * w[n1];
+            im[n1] = ((n1 == 0 ? vy0 : v[n1 + 10]) - cmu_y) * w[n1];
+        });
+    }
+    fft32_zero_tail(re, im);
+    float zr, zi;
+    ld2(TWZ + 2 * n2, zr, zi);
+    static_for<0, 32>([&](auto r_) {
+        constexpr int r = decltype(r_)::value;
+        constexpr int k1 = brev<5>(r);
+        float ar = re[r], ai = im[r];
+        if constexpr (k1 == 0) {  // row 0 is read by lane 0 of pass 2, whose table row is W_32^n2: compensate
+            const float t = ar * zr - ai * zi;
+            ai = ar * zi + ai * zr;
+            ar = t;
+        }
+        st2(EX + k1 * kExRowFloats + 2 * n2, ar, ai);
+    });
+}
+
+// ---------------------------------------------------------------------------------------------
+// Pass 2a of lane t: rows ka / kb times TW[t] / conj(TW[t]), two 16-point DIF FFTs.
+//   a[brev4(k2)]            = Z[ka + 32*k2]
+//   b[brev4((k2 + 1) % 16)] = Z[kb + 32*k2]      (the W_16^n2 modulation rotates the output index)
+// ---------------------------------------------------------------------------------------------
+PSLA_HD void pair_pass2_fft(int t, const float* __restrict__ EX, const float* __restrict__ TW, float (&ar)[16],
+                            float (&ai)[16], float (&br)[16], float (&bi)[16]) {
+    const int ka = t;
+    const int kb = (t != 0) ? 32 - t : 16;
+    const float* ra = EX + ka * kExRowFloats;
+    const float* rb = EX + kb * kExRowFloats;
+    const float* tw = TW + t * kExRowFloats;
+    static_for<0, 8>([&](auto q_) {
+        constexpr int n = 2 * decltype(q_)::value;
+        ld4(ra + 2 * n, ar[n], ai[n], ar[n + 1], ai[n + 1]);
+        ld4(rb + 2 * n, br[n], bi[n], br[n + 1], bi[n + 1]);
+    });
+    static_for<0, 8>([&](auto q_) {
+        constexpr int n = 2 * decltype(q_)::value;
+        float w0r, w0i, w1r, w1i;
+        ld4(tw + 2 * n, w0r, w0i, w1r, w1i);
+        if constexpr (n != 0) {  // TW[t][0] == 1
+            const float xr = ar[n] * w0r - ai[n] * w0i;
+            ai[n] = ar[n] * w0i + ai[n] * w0r;
+            ar[n] = xr;
+            const float yr = br[n] * w0r + bi[n] * w0i;
+            bi[n] = bi[n] * w0r - br[n] * w0i;
+            br[n] = yr;
+        }
+        const float xr = ar[n + 1] * w1r - ai[n + 1] * w1i;
+        ai[n + 1] = ar[n + 1] * w1i + ai[n + 1] * w1r;
+        ar[n + 1] = xr;
+        const float yr = br[n + 1] * w1r + bi[n + 1] * w1i;
+        bi[n + 1] = bi[n + 1] * w1r - br[n + 1] * w1i;
+        br[n + 1] = yr;
+    });
+    fft_dif<16>(ar, ai);
+    fft_dif<16>(br, bi);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Pass 2b: separation of the two real spectra + power, stored as P[bin][2h], P[bin][2h + 1].
+//   X[k] = Z[k] + conj(Z[512-k]),  Y[k] = -i * (Z[k] - conj(Z[512-k]))   (1/2 folded into the window)
+// Lanes 1..15, slot k2:  Z[t + 32*k2] = A[k2] pairs with Z[(32-t) + 32*(15-k2)] = B[(16-k2) % 16]  (A, B: natural-order
+// views of a, b).  Slots k2 < 8 give bin t + 32*k2; slots k2 >= 8 give the mirror bin (32-t) + 32*(15-k2) (|X[512-k]| =
+// |X[k]| for real input).  Lane 0 holds rows 0 and 16, whose partners sit in the SAME row: row 0 pairs A[k2] with
+// A[(16-k2) % 16] (bins 32*k2), row 16 pairs B[(k2+1) % 16] with B[16-k2] (bins 16 + 32*(15-k2)).  Both differ from
+// the generic pairing in ONE operand with the same index, so lane 0 costs 16 complex selects, no code path of its own.
+// Separate from 2a because P aliases the exchange buffers: every lane of the warp must have finished its pass-2 reads
+// before any lane stores (__syncwarp on the device, loop order on the host).
+// ---------------------------------------------------------------------------------------------
+PSLA_HD void pair_power_store(int t, int h, const float (&ar)[16], const float (&ai)[16], const float (&br)[16],
+                              const float (&bi)[16], float* __restrict__ P) {
+    const bool t0 = (t == 0);
+    float* plo = P + 4 * t + 2 * h;                          // bin t + 32*k2
+    float* phi = P + 4 * (t0 ? 16 : 32 - t) + 2 * h;         // bin hibase + 32*(15-k2)
+    static_for<0, 16>([&](auto k2_) {
+        constexpr int k2 = decltype(k2_)::value;
+        constexpr int ia = brev<4>(k2);              // A[k2]
+        constexpr int ib = brev<4>((16 - k2) % 16);  // B[(16-k2) % 16]
+        float ur, ui, vr, vi;
+        if constexpr (k2 < 8) {
+            ur = ar[ia];
+            ui = ai[ia];
+            constexpr int ia2 = brev<4>((16 - k2) % 16);  // lane 0: A[(16-k2) % 16]
+            vr = t0 ? ar[ia2] : br[ib];
+            vi = t0 ? ai[ia2] : bi[ib];
+        } else {
+            constexpr int ib2 = brev<4>((k2 + 1) % 16);  // lane 0: B[(k2+1) % 16]
+            ur = t0 ? br[ib2] : ar[ia];
+            ui = t0 ? bi[ib2] : ai[ia];
+            vr = br[ib];
+            vi = bi[ib];
+        }
+        const float xr = ur + vr, xi = ui - vi;
+        const float yr = ui + vi, yi = vr - ur;
+        const float px = xr * xr + xi * xi;
+        const float py = yr * yr + yi * yi;
+        if constexpr (k2 < 8) st2(plo + 128 * k2, px, py);
+        else st2(phi + 128 * (15 - k2), px, py);
+    });
+}
+
+// ---------------------------------------------------------------------------------------------
+// Mel projection for the 4 frames of a warp: acc[i][f] = sum_r W[off_i + r][lane] * P[start_i + r][f]
+// R0..R3 >= 0: compile-time tap counts (fully unrolled, weights zero padded); R0 < 0: run-time counts from `info`.
+// ---------------------------------------------------------------------------------------------
+struct MelView {
+    const int* start;  // [4][32]
+    const int* bin;    // [4][32]
+    const int* info;   // slot_max[4], slot_off[4]
+    const float* w;    // [rows][32]
+};
+
+template <int R, int OFF>
+PSLA_HD void mel_slot_static(int lane, const float* __restrict__ P, const float* __restrict__ w, int start, float (&acc)[kGroupFrames]) {
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    const float* p = P + 4 * start;
+    static_for<0, R>([&](auto r_) {
+        constexpr int r = decltype(r_)::value;
+        const float wv = w[32 * (OFF + r) + lane];
+        float p0, p1, p2, p3;
+        ld4(p + 4 * r, p0, p1, p2, p3);
+        a0 = fmaf(wv, p0, a0);
+        a1 = fmaf(wv, p1, a1);
+        a2 = fmaf(wv, p2, a2);
+        a3 = fmaf(wv, p3, a3);
+    });
+    acc[0] = a0;
+    acc[1] = a1;
+    acc[2] = a2;
+    acc[3] = a3;
+}
+
+template <bool SPEC>
+PSLA_HD void warp_mel(int lane, const float* __restrict__ P, const MelView& mt, float (&acc)[kMelSlots][kGroupFrames]) {
+    if constexpr (SPEC) {
+        mel_slot_static<kMelSpec0, 0>(lane, P, mt.w, mt.start[lane], acc[0]);
+        mel_slot_static<kMelSpec1, kMelSpec0>(lane, P, mt.w, mt.start[32 + lane], acc[1]);
+        mel_slot_static<kMelSpec2, kMelSpec0 + kMelSpec1>(lane, P, mt.w, mt.start[64 + lane], acc[2]);
+        mel_slot_static<kMelSpec3, kMelSpec0 + kMelSpec1 + kMelSpec2>(lane, P, mt.w, mt.start[96 + lane], acc[3]);
+    } else {
+        for (int i = 0; i < kMelSlots; ++i) {
+            const float* p = P + 4 * mt.start[32 * i + lane];
+            const float* w = mt.w + 32 * mt.info[4 + i] + lane;
+            const int rmax = mt.info[i];
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+            for (int r = 0; r < rmax; ++r) {
+                const float wv = w[32 * r];
+                float p0, p1, p2, p3;
+                ld4(p + 4 * r, p0, p1, p2, p3);
+                a0 = fmaf(wv, p0, a0);
+                a1 = fmaf(wv, p1, a1);
+                a2 = fmaf(wv, p2, a2);
+                a3 = fmaf(wv, p3, a3);
+            }
+            acc[i][0] = a0;
+            acc[i][1] = a1;
+            acc[i][2] = a2;
+            acc[i][3] = a3;
+        }
+    }
+}
+
+}  // namespace psla

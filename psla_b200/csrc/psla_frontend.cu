@@ -5,12 +5,15 @@
 // (src/dataloaders/audioset_dataset.py:88-137, 177-192), whose arithmetic is
 // torchaudio.compliance.kaldi.fbank (torchaudio/compliance/kaldi.py:514-645).
 //
-// Two kernels per forward():
-//   clip_stats_kernel  per-clip waveform sums (deterministic two-level reduction) for the whole-clip DC
-//                      removal and the mixup mean (audioset_dataset.py:92,98-99,117)
-//   fbank_tile_kernel  one CTA = 32 consecutive frames of one clip: stage the (mixed, mean-removed,
-//                      pre-emphasised) samples once in shared memory, then every warp turns 4 frames into
-//                      4 normalised output rows (see fbank_tile.cuh for the per-lane algorithm).
+// Kernels per forward():
+//   fbank_stream_kernel  persistent, one CTA of 16 autonomous warps per SM: every warp walks along its share of the
+//                        batch's frames 4 at a time -- stage 640 new (mixed, pre-emphasised) samples in its private
+//                        shared-memory window, two 512-point complex FFTs (one per half-warp, two real frames each),
+//                        power, sparse mel, log, SpecAugment fill, normalisation, 128-byte row stores
+//                        (see fbank_stream.cuh for the per-lane algorithm, stream_kernel.cuh for the kernel).
+//   clip_stats_kernel    per-clip waveform sums (deterministic two-level reduction) for the whole-clip means of
+//                        audioset_dataset.py:92,98-99,117.  Launched only for clips that need them: all clips in
+//                        exact-clip-mean mode, otherwise only mixup clips whose partner is shorter.
 // No cuFFT, no tensor cores (the mel projection is 504 non-zeros, not a dense contraction), no CPU path.
 #include <cuda_runtime.h>
 
@@ -21,7 +24,7 @@
 #include <vector>
 
 #include "../../include/psla_frontend.h"
-#include "frontend_kernels.cuh"
+#include "stream_kernel.cuh"
 #include "tables.h"
 
 // ================================================================================================
@@ -41,6 +44,9 @@ struct psla_frontend {
     int tab_floats = 0;
     size_t smem_bytes = 0;
     int fast_log = 0;
+    int exact_mean = 0;
+    bool mel_spec = false;
+    int num_sms = 0;
     int timing = 0;
     struct EvTriple {
         cudaEvent_t e[3];
@@ -90,20 +96,21 @@ struct DeviceGuard {
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+template <bool EXACT, bool MELSPEC>
+cudaError_t prepare_kernel(size_t smem) {
+    cudaError_t e = cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         static_cast<int>(smem));
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+}
+
 int upload_tables(psla_frontend* h) {
-    PackedMel pm;
-    if (!pack_mel(h->mel_dense.data(), h->nmel, kNfft, &pm)) return PSLA_E_UNSUPPORTED;
-    const int total = static_cast<int>(align_up(kTabMelW + pm.w.size(), 4));
-    std::vector<float> buf(total, 0.f);
-    for (int j = 0; j < kFrameLen; ++j) buf[kTabWin + j] = 0.5f * h->window[j];
-    build_twiddles(buf.data() + kTabTw);
-    std::memcpy(buf.data() + kTabMelStart, pm.start, sizeof(pm.start));
-    std::memcpy(buf.data() + kTabMelCount, pm.count, sizeof(pm.count));
-    std::memcpy(buf.data() + kTabSlotMax, pm.slot_max, sizeof(pm.slot_max));
-    std::memcpy(buf.data() + kTabSlotOff, pm.slot_off, sizeof(pm.slot_off));
-    std::memcpy(buf.data() + kTabMelW, pm.w.data(), pm.w.size() * sizeof(float));
-    const size_t smem = static_cast<size_t>(kSmTab + total) * sizeof(float);
-    if (smem > 113 * 1024) return PSLA_E_UNSUPPORTED;  // keep 2 CTAs / SM
+    std::vector<float> buf;
+    bool spec = false;
+    if (!build_table_buffer(h->window.data(), h->mel_dense.data(), h->nmel, &buf, &spec)) return PSLA_E_UNSUPPORTED;
+    const int total = static_cast<int>(buf.size());
+    const size_t smem = (static_cast<size_t>(total) + static_cast<size_t>(kWarpsPerCta) * kWarpFloats) * sizeof(float);
+    if (smem > 227 * 1024) return PSLA_E_UNSUPPORTED;  // tables + 16 warp windows must fit one SM
     if (h->d_tab) {
         PSLA_CUDA(h, cudaDeviceSynchronize());
         cudaFree(h->d_tab);
@@ -113,8 +120,12 @@ int upload_tables(psla_frontend* h) {
     PSLA_CUDA(h, cudaMemcpy(h->d_tab, buf.data(), total * sizeof(float), cudaMemcpyHostToDevice));
     h->tab_floats = total;
     h->smem_bytes = smem;
-    PSLA_CUDA(h, cudaFuncSetAttribute(fbank_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-    PSLA_CUDA(h, cudaFuncSetAttribute(fbank_tile_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100));
+    h->mel_spec = spec;
+    PSLA_CUDA(h, (prepare_kernel<false, false>(smem)));
+    PSLA_CUDA(h, (prepare_kernel<false, true>(smem)));
+    PSLA_CUDA(h, (prepare_kernel<true, false>(smem)));
+    PSLA_CUDA(h, (prepare_kernel<true, true>(smem)));
+    PSLA_CUDA(h, cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, h->device));
     return PSLA_OK;
 }
 
@@ -230,6 +241,7 @@ int psla_frontend_get_tables(const psla_frontend_t* h, float* window, float* mel
 size_t psla_frontend_workspace_bytes(const psla_frontend_t* h, int n_clips) {
     if (!h || n_clips < 0) return 0;
     return align_up(static_cast<size_t>(n_clips) * sizeof(ClipDesc), 256) +
+           align_up((static_cast<size_t>(n_clips) + 1) * sizeof(ClipCost), 256) +
            static_cast<size_t>(n_clips) * kStatSegs * kStatVals * sizeof(double);
 }
 
@@ -273,6 +285,12 @@ int psla_frontend_set_fast_log(psla_frontend_t* h, int enable) {
     return PSLA_OK;
 }
 
+int psla_frontend_set_exact_clip_mean(psla_frontend_t* h, int enable) {
+    if (!h) return PSLA_E_INVALID;
+    h->exact_mean = enable ? 1 : 0;
+    return PSLA_OK;
+}
+
 int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* wav_offset, const int64_t* wav_length,
                           int n_wav, const int32_t* src1,
                           const int32_t* src2, const double* lambda, const int32_t* mask, int n_clips, int target_length,
@@ -282,7 +300,7 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
     if (n_clips == 0) return PSLA_OK;
     if (!wav || !out) return PSLA_E_INVALID;
     if ((reinterpret_cast<uintptr_t>(wav) & 15) || (reinterpret_cast<uintptr_t>(out) & 3)) return PSLA_E_INVALID;
-    if (n_clips > 65535) return PSLA_E_INVALID;  // gridDim.y
+    if (n_clips > 65535) return PSLA_E_INVALID;  // gridDim.y of the statistics kernel
     const size_t need = psla_frontend_workspace_bytes(h, n_clips);
     if (!workspace || workspace_bytes < need || (reinterpret_cast<uintptr_t>(workspace) & 255)) return PSLA_E_WORKSPACE;
     if (!skip_norm && !(norm_div != 0.f)) return PSLA_E_INVALID;
@@ -293,20 +311,26 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
 
     // ---- pinned staging slot ----
     psla_frontend::Slot& slot = h->slots[h->next_slot];
-    const size_t desc_bytes = static_cast<size_t>(n_clips) * sizeof(ClipDesc);
+    const size_t desc_bytes = align_up(static_cast<size_t>(n_clips) * sizeof(ClipDesc), 256);
+    const size_t cost_bytes = align_up((static_cast<size_t>(n_clips) + 1) * sizeof(ClipCost), 256);
+    const size_t meta_bytes = desc_bytes + cost_bytes;
     if (slot.pending) {
         PSLA_CUDA(h, cudaEventSynchronize(slot.ev));
         slot.pending = false;
     }
-    if (slot.cap < desc_bytes) {
+    if (slot.cap < meta_bytes) {
         if (slot.host) cudaFreeHost(slot.host);
         slot.host = nullptr;
         slot.cap = 0;
-        const size_t cap = align_up(desc_bytes * 2, 4096);
+        const size_t cap = align_up(meta_bytes * 2, 4096);
         PSLA_CUDA(h, cudaHostAlloc(&slot.host, cap, cudaHostAllocDefault));
         slot.cap = cap;
     }
     ClipDesc* descs = static_cast<ClipDesc*>(slot.host);
+    ClipCost* costs = reinterpret_cast<ClipCost*>(static_cast<char*>(slot.host) + desc_bytes);
+    const int G = (target_length + kGroupFrames - 1) / kGroupFrames;
+    long long total_cost = 0;
+    bool any_stats = false;
 
     // ---- validate + build descriptors (errors surface synchronously, like the reference's exceptions) ----
     for (int i = 0; i < n_wav; ++i)
@@ -336,7 +360,12 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
         } else if (c != -1) {
             return PSLA_E_INVALID;
         }
-        d.aligned = ((d.off1 & 3) == 0 ? 1 : 0) | ((d.off2 & 3) == 0 ? 2 : 0);
+        d.flags = ((d.off1 & 3) == 0 ? kFlagAligned1 : 0) | ((d.off2 & 3) == 0 ? kFlagAligned2 : 0);
+        // whole-clip means are needed in exact mode, and for the zero-padded tail of a shorter mixup partner
+        if (h->exact_mean || (d.n2 > 0 && d.n2 < d.n1)) {
+            d.flags |= kFlagStats;
+            any_stats = true;
+        }
         d.pad0 = d.pad1 = 0;
         d.f0 = d.f1 = d.t0 = d.t1 = 0;
         if (mask) {
@@ -355,12 +384,39 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
         }
         const int64_t mfr = frames_of(n1);
         d.m_eff = static_cast<int>(mfr < target_length ? mfr : target_length);
+        // dead groups (4 rows that are all padding / time-masked): [a_lo, a_hi) and [b_lo, G)
+        ClipCost& cst = costs[b];
+        int b_lo = (d.m_eff + kGroupFrames - 1) / kGroupFrames, a_lo = 0, a_hi = 0;
+        if (d.t1 > d.t0) {
+            const int lo = d.t0 < d.m_eff ? d.t0 : d.m_eff, hi = d.t1 < d.m_eff ? d.t1 : d.m_eff;
+            if (hi >= d.m_eff) {  // the mask reaches the end of the computed rows: one dead run up to T
+                b_lo = (lo + kGroupFrames - 1) / kGroupFrames;
+            } else {
+                a_lo = (lo + kGroupFrames - 1) / kGroupFrames;
+                a_hi = hi / kGroupFrames;
+                if (a_hi < a_lo) a_lo = a_hi = 0;
+            }
+        }
+        if (b_lo > G) b_lo = G;
+        if (a_hi > b_lo) a_hi = b_lo;
+        if (a_lo > a_hi) a_lo = a_hi;
+        cst.cum = total_cost;
+        cst.a_lo = a_lo;
+        cst.a_hi = a_hi;
+        cst.b_lo = b_lo;
+        cst.pad = 0;
+        cst.pad2 = 0;
+        total_cost += static_cast<long long>(kLiveCost) * G - static_cast<long long>(kLiveCost - 1) * ((a_hi - a_lo) + (G - b_lo));
     }
+    costs[n_clips].cum = total_cost;
+    costs[n_clips].a_lo = costs[n_clips].a_hi = costs[n_clips].b_lo = costs[n_clips].pad = 0;
+    costs[n_clips].pad2 = 0;
 
     // ---- enqueue ----
     ClipDesc* d_desc = static_cast<ClipDesc*>(workspace);
-    double* d_part = reinterpret_cast<double*>(static_cast<char*>(workspace) + align_up(desc_bytes, 256));
-    PSLA_CUDA(h, cudaMemcpyAsync(d_desc, descs, desc_bytes, cudaMemcpyHostToDevice, stream));
+    ClipCost* d_cost = reinterpret_cast<ClipCost*>(static_cast<char*>(workspace) + desc_bytes);
+    double* d_part = reinterpret_cast<double*>(static_cast<char*>(workspace) + meta_bytes);
+    PSLA_CUDA(h, cudaMemcpyAsync(d_desc, descs, meta_bytes, cudaMemcpyHostToDevice, stream));
     PSLA_CUDA(h, cudaEventRecord(slot.ev, stream));
     slot.pending = true;
     h->next_slot = (h->next_slot + 1) % 4;
@@ -370,18 +426,25 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
         for (auto& e : ev.e) PSLA_CUDA(h, cudaEventCreate(&e));
         PSLA_CUDA(h, cudaEventRecord(ev.e[0], stream));
     }
-    clip_stats_kernel<<<dim3(kStatSegs, n_clips), 256, 0, stream>>>(wav, d_desc, d_part);
-    PSLA_CUDA(h, cudaGetLastError());
+    if (any_stats) {
+        clip_stats_kernel<<<dim3(kStatSegs, n_clips), 256, 0, stream>>>(wav, d_desc, d_part);
+        PSLA_CUDA(h, cudaGetLastError());
+        h->launches += 1;
+    }
     if (h->timing) PSLA_CUDA(h, cudaEventRecord(ev.e[1], stream));
 
-    FbankParams p;
+    StreamParams p;
     p.wav = wav;
     p.desc = d_desc;
+    p.cost = d_cost;
     p.partials = d_part;
     p.tab = h->d_tab;
     p.out = out;
+    p.total_cost = total_cost;
     p.tab_floats = h->tab_floats;
+    p.n_clips = n_clips;
     p.T = target_length;
+    p.G = G;
     p.nmel = h->nmel;
     p.norm_mean = norm_mean;
     p.norm_div = norm_div;
@@ -395,14 +458,20 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
     p.fast_log = h->fast_log;
     p.preemph = h->preemph;
     p.c1 = static_cast<float>(1.0 - static_cast<double>(h->preemph));
-    const int tiles = (target_length + kFramesPerCta - 1) / kFramesPerCta;
-    fbank_tile_kernel<<<dim3(tiles, n_clips), kThreads, h->smem_bytes, stream>>>(p);
+    const dim3 grid(h->num_sms > 0 ? h->num_sms : 148);
+    if (h->exact_mean) {
+        if (h->mel_spec) fbank_stream_kernel<true, true><<<grid, kThreads, h->smem_bytes, stream>>>(p);
+        else fbank_stream_kernel<true, false><<<grid, kThreads, h->smem_bytes, stream>>>(p);
+    } else {
+        if (h->mel_spec) fbank_stream_kernel<false, true><<<grid, kThreads, h->smem_bytes, stream>>>(p);
+        else fbank_stream_kernel<false, false><<<grid, kThreads, h->smem_bytes, stream>>>(p);
+    }
     PSLA_CUDA(h, cudaGetLastError());
     if (h->timing) {
         PSLA_CUDA(h, cudaEventRecord(ev.e[2], stream));
         h->timed.push_back(ev);
     }
-    h->launches += 2;
+    h->launches += 1;
     return PSLA_OK;
 }
 

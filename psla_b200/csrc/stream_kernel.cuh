@@ -1,0 +1,621 @@
+// Device code of libpsla_frontend.so: the per-clip statistics kernel and the warp-autonomous streaming fbank kernel.
+// (Host side / C ABI: psla_frontend.cu.  Per-lane FFT / mel phases: fbank_stream.cuh.)
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include "fbank_stream.cuh"
+
+namespace psla {
+
+// ------------------------------------------------------------------------------------------------
+// Device-side data
+// ------------------------------------------------------------------------------------------------
+struct alignas(16) ClipDesc {  // 64 bytes, one per output clip
+    long long off1, off2;  // start sample of the primary / partner waveform inside `wav`
+    int n1, n2;            // lengths; n2 == 0 means no mixup
+    float l1, l2;          // fp32(lambda), fp32(1 - lambda) (the latter rounded from the float64 difference)
+    int f0, f1;            // frequency mask [f0, f1)
+    int t0, t1;            // time mask [t0, t1)
+    int m_eff;             // min(num_frames(n1), target_length): rows that hold real features
+    int flags;             // bit 0: off1 % 4 == 0, bit 1: off2 % 4 == 0 (128-bit loads allowed), bit 2: clip statistics needed
+    int pad0, pad1;
+};
+static_assert(sizeof(ClipDesc) == 64, "ClipDesc layout");
+constexpr int kFlagAligned1 = 1, kFlagAligned2 = 2, kFlagStats = 4;
+
+// Work partition: a group (4 output rows) costs kLiveCost if any of its rows carries computed features, 1 if all four
+// are padding / time-masked (constant rows).  Dead groups of a clip are [a_lo, a_hi) and [b_lo, G).
+struct alignas(16) ClipCost {  // 32 bytes; entry n_clips holds the total in `cum`
+    long long cum;  // cost of all clips before this one
+    int a_lo, a_hi, b_lo, pad;
+    long long pad2;
+};
+static_assert(sizeof(ClipCost) == 32, "ClipCost layout");
+constexpr int kLiveCost = 32;
+
+constexpr int kStatSegs = 8;  // partial sums per clip
+constexpr int kStatVals = 3;  // sum(w1), sum(w2), sum(w2[0:min(n1,n2)])
+
+constexpr int kWarpsPerCta = 16;
+constexpr int kThreads = kWarpsPerCta * 32;
+
+struct StreamParams {
+    const float* wav;
+    const ClipDesc* desc;
+    const ClipCost* cost;
+    const double* partials;
+    const float* tab;
+    float* out;
+    long long total_cost;
+    int tab_floats;
+    int n_clips;
+    int T;  // target_length
+    int G;  // groups per clip = ceil(T / 4)
+    int nmel;
+    float norm_mean, norm_div, norm_rdiv, fill;  // fill = (0 - mean) / div in IEEE fp32 (0 if skip_norm)
+    int skip_norm;
+    int fast_log;
+    float preemph, c1;
+};
+
+__device__ __forceinline__ ClipDesc load_desc(const ClipDesc* __restrict__ p) {
+    union {
+        ClipDesc d;
+        int4 v[4];
+    } u;
+    const int4* src = reinterpret_cast<const int4*>(p);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) u.v[i] = __ldg(src + i);
+    return u.d;
+}
+__device__ __forceinline__ ClipCost load_cost(const ClipCost* __restrict__ p) {
+    union {
+        ClipCost c;
+        int4 v[2];
+    } u;
+    const int4* src = reinterpret_cast<const int4*>(p);
+    u.v[0] = __ldg(src);
+    u.v[1] = __ldg(src + 1);
+    return u.c;
+}
+
+// 4 consecutive samples [i, i+4) of a waveform of n samples, zeros past the end
+__device__ __forceinline__ float4 load4(const float* __restrict__ w, int i, int n, bool aligned) {
+    if (aligned && i + 3 < n) return __ldg(reinterpret_cast<const float4*>(w + i));
+    float4 v;
+    v.x = (i < n) ? __ldg(w + i) : 0.f;
+    v.y = (i + 1 < n) ? __ldg(w + i + 1) : 0.f;
+    v.z = (i + 2 < n) ? __ldg(w + i + 2) : 0.f;
+    v.w = (i + 3 < n) ? __ldg(w + i + 3) : 0.f;
+    return v;
+}
+
+// sum of w[lo, hi) by one 256-thread CTA's thread `tid` (strided float4s, 4 loads in flight)
+__device__ __forceinline__ float strided_sum(const float* __restrict__ w, int lo, int hi, int tid, bool aligned) {
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    int i = lo + 4 * tid;
+    if (aligned) {
+        for (; i + 3 * 1024 + 3 < hi; i += 4 * 1024) {
+            const float4 a = __ldg(reinterpret_cast<const float4*>(w + i));
+            const float4 b = __ldg(reinterpret_cast<const float4*>(w + i + 1024));
+            const float4 c = __ldg(reinterpret_cast<const float4*>(w + i + 2048));
+            const float4 d = __ldg(reinterpret_cast<const float4*>(w + i + 3072));
+            s0 += (a.x + a.y) + (a.z + a.w);
+            s1 += (b.x + b.y) + (b.z + b.w);
+            s2 += (c.x + c.y) + (c.z + c.w);
+            s3 += (d.x + d.y) + (d.z + d.w);
+        }
+    }
+    for (; i < hi; i += 1024) {
+        const float4 v = load4(w, i, hi, aligned);
+        s0 += (v.x + v.y) + (v.z + v.w);
+    }
+    return (s0 + s1) + (s2 + s3);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Kernel 1 (only launched when some clip needs it): per-clip sums for the whole-clip means of
+// audioset_dataset.py:92 / :98-99 / :117.  grid = (kStatSegs, B), block = 256.  Deterministic: fixed partition, fixed
+// reduction tree; the streaming kernel adds the kStatSegs partials in a fixed order.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) clip_stats_kernel(const float* __restrict__ wav, const ClipDesc* __restrict__ desc,
+                                                         double* __restrict__ partials) {
+    const int b = blockIdx.y, g = blockIdx.x, tid = threadIdx.x;
+    const ClipDesc d = load_desc(desc + b);
+    if (!(d.flags & kFlagStats)) return;
+    float s1, s2 = 0.f, s2c = 0.f;
+    {
+        const int seg = ((d.n1 + 4 * kStatSegs - 1) / (4 * kStatSegs)) * 4;
+        const int lo = min(d.n1, g * seg), hi = min(d.n1, lo + seg);
+        s1 = strided_sum(wav + d.off1, lo, hi, tid, d.flags & kFlagAligned1);
+    }
+    if (d.n2 > 0) {
+        const int nmin = min(d.n1, d.n2);
+        const int seg = ((d.n2 + 4 * kStatSegs - 1) / (4 * kStatSegs)) * 4;
+        const int lo = min(d.n2, g * seg), hi = min(d.n2, lo + seg);
+        const bool al = (d.flags & kFlagAligned2) != 0;
+        s2 = strided_sum(wav + d.off2, lo, hi, tid, al);
+        if (nmin >= hi) s2c = s2;                                               // segment entirely kept
+        else if (nmin > lo) s2c = strided_sum(wav + d.off2, lo, nmin, tid, al);  // the one straddling segment
+    }
+    __shared__ double red[8][kStatVals];
+    double v0 = s1, v1 = s2, v2 = s2c;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        v0 += __shfl_xor_sync(0xffffffffu, v0, o);
+        v1 += __shfl_xor_sync(0xffffffffu, v1, o);
+        v2 += __shfl_xor_sync(0xffffffffu, v2, o);
+    }
+    if ((tid & 31) == 0) {
+        red[tid >> 5][0] = v0;
+        red[tid >> 5][1] = v1;
+        red[tid >> 5][2] = v2;
+    }
+    __syncthreads();
+    if (tid < kStatVals) {
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) s += red[w][tid];
+        partials[(static_cast<size_t>(b) * kStatSegs + g) * kStatVals + tid] = s;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Per-clip state of a warp.  It lives in the warp's shared-memory window, not in registers: the FFT phases need
+// almost the whole 128-register budget, and anything loop-carried would be spilled to local memory around them.
+// Every use is a volatile shared-memory read (so the compiler cannot cache it in a register across the FFT).
+// ------------------------------------------------------------------------------------------------
+enum ClipStateWord {
+    CS_N1 = 0, CS_NMIN, CS_L1, CS_L2, CS_SUB1, CS_MEAN2, CS_MIXMEAN, CS_FLAGS, CS_F0, CS_F1, CS_T0, CS_T1, CS_MEFF,
+    CS_ALO, CS_AHI, CS_BLO, CS_OFF1 /* 2 words */, CS_OFF1_HI, CS_OFF2 /* 2 words */, CS_OFF2_HI, CS_END
+};
+static_assert(CS_END <= kCsWords && CS_OFF1 % 2 == 0 && CS_OFF2 % 2 == 0, "clip-state layout");
+constexpr int kCsMix = 8;  // CS_FLAGS: kFlagAligned1 | kFlagAligned2 | kCsMix
+
+__device__ __forceinline__ int cs_i(const int* cs, int w) { return *reinterpret_cast<const volatile int*>(cs + w); }
+__device__ __forceinline__ float cs_f(const int* cs, int w) { return __int_as_float(cs_i(cs, w)); }
+__device__ __forceinline__ long long cs_ll(const int* cs, int w) { return *reinterpret_cast<const volatile long long*>(cs + w); }
+
+// ------------------------------------------------------------------------------------------------
+// Waveform conditioning of one clip (audioset_dataset.py:91-117).
+//   EXACT   x = (l1*(a - mean1) + l2*(c' - mean2)) - mixmean in the reference's fp32 op order, c' the partner zero-padded
+//           AFTER its mean removal (:104-106) or cut (:109); the three means come from clip_stats_kernel.
+//   fused   every constant the reference subtracts from the whole clip is removed again by the per-frame DC removal
+//           (kaldi.py:183-186), so x + const gives the same features (up to fp32 rounding).  The constant used here is
+//           the clip's first sample(s) instead of the mean -- no pass over the clip is needed, and the values stay
+//           small when the recording has a DC offset:   x' = l1*a + l2*c - (l1*a[0] + l2*c[0]).
+//           The one place a mean survives is the zero-padded tail of a SHORTER partner: there c' - mean2 = 0, i.e.
+//           c is replaced by mean2 (clip statistics are computed for those clips only).
+// FULL: the staged range lies inside both waveforms and both are 16-byte aligned -- no bounds checks, no selects.
+// ------------------------------------------------------------------------------------------------
+struct MixState {
+    const float* w1;
+    const float* w2;
+    float l1, l2;
+    float sub1;     // EXACT: mean1;  fused: K = l1*a[0] (+ l2*c[0])
+    float mean2;    // EXACT: mean2;  fused: mean2 where the partner is shorter (tail fill)
+    float mixmean;  // EXACT only
+    int n1, nmin;
+    bool mix, al1, al2;
+};
+
+__device__ __forceinline__ MixState load_mix(const int* cs, const float* wav) {
+    MixState m;
+    const int fl = cs_i(cs, CS_FLAGS);
+    m.w1 = wav + cs_ll(cs, CS_OFF1);
+    m.w2 = wav + cs_ll(cs, CS_OFF2);
+    m.l1 = cs_f(cs, CS_L1);
+    m.l2 = cs_f(cs, CS_L2);
+    m.sub1 = cs_f(cs, CS_SUB1);
+    m.mean2 = cs_f(cs, CS_MEAN2);
+    m.mixmean = cs_f(cs, CS_MIXMEAN);
+    m.n1 = cs_i(cs, CS_N1);
+    m.nmin = cs_i(cs, CS_NMIN);
+    m.mix = (fl & kCsMix) != 0;
+    m.al1 = (fl & kFlagAligned1) != 0;
+    m.al2 = (fl & kFlagAligned2) != 0;
+    return m;
+}
+
+// the group window [S0, S0 + 880) can be staged without bounds checks
+__device__ __forceinline__ bool window_full(const MixState& m, int S0) {
+    return m.al1 && S0 + kGroupSamples <= m.n1 && (!m.mix || (m.al2 && S0 + kGroupSamples <= m.nmin));
+}
+
+template <bool EXACT, bool FULL>
+__device__ __forceinline__ float mix_sample(const MixState& m, float a, float c, int s) {
+    if (!FULL && s >= m.n1) return 0.f;
+    if (!m.mix) return __fsub_rn(a, m.sub1);
+    if (EXACT) {
+        const float v1 = __fsub_rn(a, m.sub1);
+        const float v2 = (FULL || s < m.nmin) ? __fsub_rn(c, m.mean2) : 0.f;
+        return __fsub_rn(__fadd_rn(__fmul_rn(m.l1, v1), __fmul_rn(m.l2, v2)), m.mixmean);
+    } else {
+        const float ce = (FULL || s < m.nmin) ? c : m.mean2;
+        return fmaf(m.l1, a, fmaf(m.l2, ce, -m.sub1));
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Warp-private staging of the group window.  U0 = first window sample staged (0: cold start, 7 float4 per lane;
+// 240: steady state, 5 float4 per lane).  issue() only loads (so the latency can hide behind the mel / epilogue of the
+// previous group), commit() conditions the samples and writes
+//   D[dpad(u)] = x[u] - p*x[u-1],  BS[u/16] = sum of 16 samples,  XS[u/160] = (1-p)*x[u]  (u % 160 == 0).
+// `carry` is x of the last sample staged so far (pre-emphasis neighbour of the next staged sample).
+// ------------------------------------------------------------------------------------------------
+template <int U0>
+struct StageGeom {
+    static constexpr int kFloat4 = (kGroupSamples - U0) / 4;  // 220 or 160
+    static constexpr int kIters = (kFloat4 + 31) / 32;        // 7 or 5
+    static constexpr int kLastLane = (kFloat4 - 1) % 32;      // lane holding the window's last float4
+};
+
+template <int U0, bool FULL, int NIT>
+__device__ __forceinline__ void stage_issue(const MixState& m, int S0, int lane, float4 (&a)[NIT], float4 (&c)[NIT]) {
+#pragma unroll
+    for (int it = 0; it < NIT; ++it) {
+        const int L = lane + 32 * it;
+        const int s = S0 + U0 + 4 * L;
+        a[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+        c[it] = a[it];
+        if ((it + 1) * 32 <= StageGeom<U0>::kFloat4 || L < StageGeom<U0>::kFloat4) {
+            if (FULL) {
+                a[it] = __ldg(reinterpret_cast<const float4*>(m.w1 + s));
+                if (m.mix) c[it] = __ldg(reinterpret_cast<const float4*>(m.w2 + s));
+            } else {
+                a[it] = load4(m.w1, s, m.n1, m.al1);
+                if (m.mix) c[it] = load4(m.w2, s, m.nmin, m.al2);
+            }
+        }
+    }
+}
+
+template <bool EXACT, int U0, bool FULL, int NIT>
+__device__ __forceinline__ void stage_commit(const MixState& m, int S0, int lane, float pe, float c1, const float4 (&a)[NIT],
+                                             const float4 (&c)[NIT], float* __restrict__ D, float* __restrict__ BS,
+                                             float* __restrict__ XS, float& carry) {
+    float last_w = 0.f;
+#pragma unroll
+    for (int it = 0; it < NIT; ++it) {
+        const int L = lane + 32 * it;
+        const int u = U0 + 4 * L;
+        const int s = S0 + u;
+        const bool in = ((it + 1) * 32 <= StageGeom<U0>::kFloat4) || L < StageGeom<U0>::kFloat4;
+        float4 x;
+        x.x = mix_sample<EXACT, FULL>(m, a[it].x, c[it].x, s);
+        x.y = mix_sample<EXACT, FULL>(m, a[it].y, c[it].y, s + 1);
+        x.z = mix_sample<EXACT, FULL>(m, a[it].z, c[it].z, s + 2);
+        x.w = mix_sample<EXACT, FULL>(m, a[it].w, c[it].w, s + 3);
+        float prev = __shfl_up_sync(0xffffffffu, x.w, 1);
+        if (lane == 0) prev = carry;
+        carry = __shfl_sync(0xffffffffu, x.w, 31);
+        last_w = x.w;
+        float s4 = (x.x + x.y) + (x.z + x.w);
+        s4 += __shfl_xor_sync(0xffffffffu, s4, 1);
+        s4 += __shfl_xor_sync(0xffffffffu, s4, 2);
+        if (in) {
+            float4 dd;
+            dd.x = fmaf(-pe, prev, x.x);
+            dd.y = fmaf(-pe, x.x, x.y);
+            dd.z = fmaf(-pe, x.y, x.z);
+            dd.w = fmaf(-pe, x.z, x.w);
+            *reinterpret_cast<float4*>(D + u + 16 * ((u >= 320) + (u >= 640))) = dd;
+            if ((lane & 3) == 0) BS[U0 / 16 + (L >> 2)] = s4;
+            // u % 160 == 0  <=>  (U0/4 + L) % 40 == 0: at most one lane per iteration, known at compile time
+            const int q = (U0 / 4 + 32 * it + 39) / 40;  // first multiple of 40 at or after this iteration's first float4
+            if (U0 / 4 + L == 40 * q) XS[q] = c1 * x.x;
+        }
+    }
+    if (StageGeom<U0>::kLastLane != 31) carry = __shfl_sync(0xffffffffu, last_w, StageGeom<U0>::kLastLane);
+}
+
+// the 240 samples (and their block sums / frame-start values) the next group shares with this one move to the front
+__device__ __forceinline__ void stage_shift(int lane, float* __restrict__ D, float* __restrict__ BS, float* __restrict__ XS) {
+    if (lane < 30) {
+        const float4 v0 = *reinterpret_cast<const float4*>(D + dpad(kStepSamples) + 4 * lane);
+        const float4 v1 = *reinterpret_cast<const float4*>(D + dpad(kStepSamples) + 4 * (lane + 30));
+        *reinterpret_cast<float4*>(D + 4 * lane) = v0;
+        *reinterpret_cast<float4*>(D + 4 * (lane + 30)) = v1;
+    }
+    const float bsv = BS[kStepSamples / 16 + (lane < 15 ? lane : 0)];
+    const float xsv = XS[4 + (lane & 1)];
+    if (lane < 15) BS[lane] = bsv;
+    if (lane < 2) XS[lane] = xsv;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Work partition helpers (see ClipCost)
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int cost_before(int a_lo, int a_hi, int b_lo, int g) {  // cost of groups [0, g) of the clip
+    const int d1 = min(max(g, a_lo), a_hi) - a_lo;
+    const int d2 = max(g, b_lo) - b_lo;
+    return kLiveCost * g - (kLiveCost - 1) * (d1 + d2);
+}
+__device__ __forceinline__ bool group_dead(const int* cs, int g) {
+    return (g >= cs_i(cs, CS_ALO) && g < cs_i(cs, CS_AHI)) || g >= cs_i(cs, CS_BLO);
+}
+
+// first group (b, g) in clip-major order whose preceding cost is >= target; returns that preceding cost
+__device__ __forceinline__ long long find_start(const ClipCost* __restrict__ cost, int n_clips, int G, long long target, int& b_out,
+                                                int& g_out) {
+    int lo = 0, hi = n_clips;  // largest b with cum[b] <= target (cum[0] == 0)
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (__ldg(&cost[mid].cum) <= target) lo = mid;
+        else hi = mid - 1;
+    }
+    b_out = lo;
+    g_out = 0;
+    const ClipCost c = load_cost(cost + lo);
+    if (lo >= n_clips) return c.cum;
+    const int rem = static_cast<int>(target - c.cum);
+    if (rem <= 0) return c.cum;
+    int glo = 1, ghi = G;  // smallest g with cost_before(g) >= rem  (cost_before(G) > rem)
+    while (glo < ghi) {
+        const int mid = (glo + ghi) >> 1;
+        if (cost_before(c.a_lo, c.a_hi, c.b_lo, mid) >= rem) ghi = mid;
+        else glo = mid + 1;
+    }
+    if (glo >= G) {
+        b_out = lo + 1;
+        return __ldg(&cost[lo + 1].cum);
+    }
+    g_out = glo;
+    return c.cum + cost_before(c.a_lo, c.a_hi, c.b_lo, glo);
+}
+
+__device__ __forceinline__ void store_fill_rows(float* __restrict__ out, int row0, int T, int nmel, int lane, float fill) {
+#pragma unroll
+    for (int q = 0; q < kGroupFrames; ++q) {
+        if (row0 + q >= T) break;
+        float* row = out + static_cast<size_t>(row0 + q) * nmel;
+#pragma unroll
+        for (int i = 0; i < kMelSlots; ++i)
+            if (lane + 32 * i < nmel) __stcs(row + lane + 32 * i, fill);
+    }
+}
+
+// load a clip's descriptor, derive its conditioning constants, park everything in the warp's clip-state words
+template <bool EXACT>
+__device__ __forceinline__ void enter_clip(const StreamParams& p, int b, int lane, int* cs) {
+    const ClipDesc d = load_desc(p.desc + b);
+    const ClipCost cc = load_cost(p.cost + b);
+    const bool mix = d.n2 > 0;
+    const int nmin = min(d.n1, d.n2);
+    float sub1 = 0.f, mean2 = 0.f, mixmean = 0.f;
+    if (d.flags & kFlagStats) {  // whole-clip means from the statistics kernel's partial sums (fixed tree)
+        const double* ps = p.partials + static_cast<size_t>(b) * kStatSegs * kStatVals;
+        double s1 = 0.0, s2 = 0.0, s2c = 0.0;
+        if (lane < kStatSegs) {
+            s1 = ps[lane * kStatVals];
+            s2 = ps[lane * kStatVals + 1];
+            s2c = ps[lane * kStatVals + 2];
+        }
+#pragma unroll
+        for (int o = kStatSegs / 2; o > 0; o >>= 1) {
+            s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+            s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+            s2c += __shfl_xor_sync(0xffffffffu, s2c, o);
+        }
+        s1 = __shfl_sync(0xffffffffu, s1, 0);
+        s2 = __shfl_sync(0xffffffffu, s2, 0);
+        s2c = __shfl_sync(0xffffffffu, s2c, 0);
+        const float mean1 = static_cast<float>(s1 / d.n1);
+        if (mix) mean2 = static_cast<float>(s2 / d.n2);
+        if (EXACT) {
+            sub1 = mean1;
+            if (mix) {  // mean over n1 samples of l1*(w1-mean1) + l2*(w2'-mean2), w2' zero-padded / cut to n1
+                const double r1 = s1 - static_cast<double>(d.n1) * mean1;
+                const double r2 = s2c - static_cast<double>(nmin) * mean2;
+                mixmean = static_cast<float>((static_cast<double>(d.l1) * r1 + static_cast<double>(d.l2) * r2) / d.n1);
+            }
+        }
+    }
+    if (!EXACT) {
+        const float a0 = __ldg(p.wav + d.off1);
+        sub1 = mix ? fmaf(d.l1, a0, d.l2 * __ldg(p.wav + d.off2)) : a0;
+    }
+    __syncwarp();
+    if (lane == 0) {
+        cs[CS_N1] = d.n1;
+        cs[CS_NMIN] = nmin;
+        cs[CS_L1] = __float_as_int(d.l1);
+        cs[CS_L2] = __float_as_int(d.l2);
+        cs[CS_SUB1] = __float_as_int(sub1);
+        cs[CS_MEAN2] = __float_as_int(mean2);
+        cs[CS_MIXMEAN] = __float_as_int(mixmean);
+        cs[CS_FLAGS] = (d.flags & (kFlagAligned1 | kFlagAligned2)) | (mix ? kCsMix : 0);
+        cs[CS_F0] = d.f0;
+        cs[CS_F1] = d.f1;
+        cs[CS_T0] = d.t0;
+        cs[CS_T1] = d.t1;
+        cs[CS_MEFF] = d.m_eff;
+        cs[CS_ALO] = cc.a_lo;
+        cs[CS_AHI] = cc.a_hi;
+        cs[CS_BLO] = cc.b_lo;
+        *reinterpret_cast<long long*>(cs + CS_OFF1) = d.off1;
+        *reinterpret_cast<long long*>(cs + CS_OFF2) = d.off2;
+    }
+    __syncwarp();
+}
+
+// log floor, SpecAugment fill, normalisation, coalesced streaming stores of the group's 4 rows
+template <bool FASTLOG>
+__device__ __forceinline__ void epilogue(const StreamParams& p, const int* cs, const int* mel_bin, int lane, int f0, float* __restrict__ out,
+                                         const float (&acc)[kMelSlots][kGroupFrames]) {
+    const float eps = 1.1920928955078125e-07f;    // kaldi.py:22
+    const float log_eps = -15.9423847198486328f;  // fp32 log(eps): what max(x, eps).log() gives on the floor
+    const float mean = p.skip_norm ? 0.f : p.norm_mean;
+    const float div = p.skip_norm ? 1.f : p.norm_div;
+    const float rdiv = p.skip_norm ? 1.f : p.norm_rdiv;
+    const int mf0 = cs_i(cs, CS_F0), mf1 = cs_i(cs, CS_F1), t0 = cs_i(cs, CS_T0), t1 = cs_i(cs, CS_T1), m_eff = cs_i(cs, CS_MEFF);
+    int mbin[kMelSlots];
+    bool keep[kMelSlots];  // column survives the frequency mask
+#pragma unroll
+    for (int i = 0; i < kMelSlots; ++i) {
+        mbin[i] = mel_bin[32 * i + lane];
+        keep[i] = !(mbin[i] >= mf0 && mbin[i] < mf1);
+    }
+#pragma unroll
+    for (int q = 0; q < kGroupFrames; ++q) {
+        const int row = f0 + q;
+        const bool rlive = row < m_eff && !(row >= t0 && row < t1);
+        if (row < p.T) {
+            float* orow = out + static_cast<size_t>(row) * p.nmel;
+#pragma unroll
+            for (int i = 0; i < kMelSlots; ++i) {
+                const float e = acc[i][q];
+                float v;
+                if (FASTLOG) {
+                    const float lg = (e > eps) ? __logf(e) : log_eps;
+                    // (lg - mean) / div as a Newton-corrected multiply by 1/div: correctly rounded but for rare
+                    // last-bit cases; live cells only need 1e-3, the fill constant is the exact IEEE quotient
+                    const float x = __fsub_rn(lg, mean);
+                    const float q0 = x * rdiv;
+                    v = fmaf(fmaf(-q0, div, x), rdiv, q0);
+                } else {
+                    const float lg = logf(fmaxf(e, eps));
+                    v = p.skip_norm ? lg : __fdiv_rn(__fsub_rn(lg, p.norm_mean), p.norm_div);
+                }
+                if (mbin[i] >= 0) __stcs(orow + mbin[i], (rlive && keep[i]) ? v : p.fill);
+            }
+        }
+    }
+}
+
+// one live group: frame means, pass 1, (shift), pass 2, power, (prefetch), mel, epilogue, (commit)
+template <bool EXACT, bool MELSPEC, bool FULLNEXT>
+__device__ __forceinline__ void process_group(const StreamParams& p, const float* TAB, float* WS, int lane, int f0, bool next_live,
+                                              float* __restrict__ out, float& carry) {
+    float* D = WS + kWsD;
+    float* BS = WS + kWsBS;
+    float* XS = WS + kWsXS;
+    const int* cs = reinterpret_cast<const int*>(WS + kWsCS);
+    float* EX = WS + kWsEX;
+    const int h = lane >> 4, n2 = lane & 15;
+    const int S0 = f0 * kFrameShift;
+
+    // per-frame means (kaldi.py:183-186) from the 16-sample block sums: lane 8 f + j adds 3 (4) blocks, xor tree
+    float cmu_x, cmu_y;
+    {
+        const float* bs = BS + 10 * (lane >> 3) + (lane & 7);
+        float a = (bs[0] + bs[8]) + bs[16];
+        if ((lane & 7) == 0) a += bs[24];
+        a += __shfl_xor_sync(0xffffffffu, a, 1);
+        a += __shfl_xor_sync(0xffffffffu, a, 2);
+        a += __shfl_xor_sync(0xffffffffu, a, 4);
+        const float cmu = p.c1 * (a * (1.0f / kFrameLen));
+        cmu_x = __shfl_sync(0xffffffffu, cmu, 16 * h);
+        cmu_y = __shfl_sync(0xffffffffu, cmu, 16 * h + 8);
+    }
+    float* EXp = EX + h * kExPairFloats;
+    pair_pass1(n2, h, D, XS, TAB + kTabWin, TAB + kTabTwz, EXp, cmu_x, cmu_y);
+    __syncwarp();
+    if (next_live) stage_shift(lane, D, BS, XS);
+    {
+        float ar[16], ai[16], br[16], bi[16];
+        pair_pass2_fft(n2, EXp, TAB + kTabTw, ar, ai, br, bi);
+        __syncwarp();  // P aliases EX: all reads done before any write
+        pair_power_store(n2, h, ar, ai, br, bi, EX);
+    }
+    __syncwarp();
+    constexpr int NIT = StageGeom<kOverlapSamples>::kIters;
+    float4 ra[NIT], rc[NIT];
+    if (next_live) {
+        const MixState m = load_mix(cs, p.wav);
+        stage_issue<kOverlapSamples, FULLNEXT>(m, S0 + kStepSamples, lane, ra, rc);
+    }
+    float acc[kMelSlots][kGroupFrames];
+    {
+        MelView mt;
+        mt.start = reinterpret_cast<const int*>(TAB + kTabMelStart);
+        mt.bin = reinterpret_cast<const int*>(TAB + kTabMelBin);
+        mt.info = reinterpret_cast<const int*>(TAB + kTabMelInfo);
+        mt.w = TAB + kTabMelW;
+        warp_mel<MELSPEC>(lane, EX, mt, acc);
+    }
+    const int* mel_bin = reinterpret_cast<const int*>(TAB + kTabMelBin);
+    if (p.fast_log) epilogue<true>(p, cs, mel_bin, lane, f0, out, acc);
+    else epilogue<false>(p, cs, mel_bin, lane, f0, out, acc);
+    if (next_live) {
+        const MixState m = load_mix(cs, p.wav);
+        stage_commit<EXACT, kOverlapSamples, FULLNEXT>(m, S0 + kStepSamples, lane, p.preemph, p.c1, ra, rc, D, BS, XS, carry);
+    }
+    __syncwarp();
+}
+
+// ------------------------------------------------------------------------------------------------
+// Kernel 2: the streaming kernel.  grid = one CTA per SM, block = 16 warps, no CTA barrier after the table load.
+// Warp r of W owns the groups whose preceding cost lies in [r*C/W, (r+1)*C/W)  (clip-major order).
+// ------------------------------------------------------------------------------------------------
+template <bool EXACT, bool MELSPEC>
+__global__ void __launch_bounds__(kThreads, 1) fbank_stream_kernel(const StreamParams p) {
+    extern __shared__ __align__(16) float smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    float* TAB = smem;
+    float* WS = smem + p.tab_floats + warp * kWarpFloats;
+    int* cs = reinterpret_cast<int*>(WS + kWsCS);
+    {
+        const float4* src = reinterpret_cast<const float4*>(p.tab);
+        float4* dst = reinterpret_cast<float4*>(TAB);
+        for (int i = tid; i < p.tab_floats / 4; i += kThreads) dst[i] = __ldg(src + i);
+    }
+    __syncthreads();
+
+    // ---- this warp's share of the work ----
+    int b, g, budget;
+    {
+        const long long W = static_cast<long long>(gridDim.x) * kWarpsPerCta;
+        const long long r = static_cast<long long>(warp) * gridDim.x + blockIdx.x;  // neighbouring ranges on different SMs
+        const long long c_lo = p.total_cost * r / W, c_hi = p.total_cost * (r + 1) / W;
+        if (c_lo >= c_hi) return;
+        const long long start_cost = find_start(p.cost, p.n_clips, p.G, c_lo, b, g);
+        budget = static_cast<int>(c_hi - start_cost);  // groups are taken while the cost consumed so far is < budget
+    }
+    int loaded_b = -1;
+    bool staged = false;  // the window holds the samples of group g
+    float carry = 0.f;
+
+    while (b < p.n_clips && budget > 0) {
+        if (b != loaded_b) {
+            enter_clip<EXACT>(p, b, lane, cs);
+            loaded_b = b;
+            staged = false;
+        }
+        const int f0 = kGroupFrames * g;
+        float* out = p.out + static_cast<size_t>(b) * p.T * p.nmel;
+        if (group_dead(cs, g)) {
+            store_fill_rows(out, f0, p.T, p.nmel, lane, p.fill);
+            budget -= 1;
+            staged = false;
+        } else {
+            const int S0 = f0 * kFrameShift;
+            if (!staged) {  // cold start of a run of groups
+                const MixState m = load_mix(cs, p.wav);
+                constexpr int NIT0 = StageGeom<0>::kIters;
+                float4 ra[NIT0], rc[NIT0];
+                carry = 0.f;
+                stage_issue<0, false>(m, S0, lane, ra, rc);
+                stage_commit<EXACT, 0, false>(m, S0, lane, p.preemph, p.c1, ra, rc, WS + kWsD, WS + kWsBS, WS + kWsXS, carry);
+                __syncwarp();
+            }
+            budget -= kLiveCost;
+            const bool next_live = (g + 1 < p.G) && !group_dead(cs, g + 1) && budget > 0;
+            bool full_next = false;
+            if (next_live) {
+                const MixState m = load_mix(cs, p.wav);
+                full_next = window_full(m, S0 + kStepSamples);
+            }
+            if (full_next) process_group<EXACT, MELSPEC, true>(p, TAB, WS, lane, f0, next_live, out, carry);
+            else process_group<EXACT, MELSPEC, false>(p, TAB, WS, lane, f0, next_live, out, carry);
+            staged = next_live;
+        }
+        if (++g == p.G) {
+            g = 0;
+            ++b;
+        }
+    }
+}
+
+}  // namespace psla

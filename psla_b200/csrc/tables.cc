@@ -47,53 +47,86 @@ void build_mel_dense(float* mel, int num_bins, int nfft, float sample_rate, floa
     }
 }
 
-void build_twiddles(float* tw) {
-    for (int k1 = 0; k1 < 32; ++k1)
-        for (int n2 = 0; n2 < 16; ++n2) {
-            const double a = -2.0 * 3.14159265358979323846 * static_cast<double>((k1 * n2) % 512) / 512.0;
-            tw[2 * (k1 * 16 + n2)] = static_cast<float>(std::cos(a));
-            tw[2 * (k1 * 16 + n2) + 1] = static_cast<float>(std::sin(a));
-        }
-}
-
-bool pack_mel(const float* dense, int num_bins, int nfft, PackedMel* out) {
-    const int nb = nfft / 2;
+bool build_table_buffer(const float* window, const float* mel_dense, int num_bins, std::vector<float>* buf, bool* mel_spec) {
+    const int nb = kNfft / 2;
     if (num_bins > kMaxMel || num_bins < 1) return false;
-    std::memset(out->start, 0, sizeof(out->start));
-    std::memset(out->count, 0, sizeof(out->count));
+    // ---- sparse structure of the mel matrix ----
+    int start[kMaxMel] = {0}, count[kMaxMel] = {0};
     for (int j = 0; j < num_bins; ++j) {
         int first = -1, last = -1;
         for (int k = 0; k < nb; ++k)
-            if (dense[j * nb + k] != 0.f) {
+            if (mel_dense[j * nb + k] != 0.f) {
                 if (first < 0) first = k;
                 last = k;
             }
         if (first < 0) continue;  // empty row (row 3 at 16 kHz / 128 bins): log floor only
         for (int k = first; k <= last; ++k)
-            if (dense[j * nb + k] == 0.f) return false;
+            if (mel_dense[j * nb + k] == 0.f) return false;
         if (last - first + 1 > kMelMaxCount) return false;
-        out->start[j] = static_cast<short>(first);
-        out->count[j] = static_cast<short>(last - first + 1);
+        start[j] = first;
+        count[j] = last - first + 1;
     }
-    int off = 0;
+    int slot_max[kMelSlots], slot_off[kMelSlots], rows = 0;
     for (int i = 0; i < kMelSlots; ++i) {
         int mx = 0;
         for (int l = 0; l < 32; ++l) {
             const int j = l + 32 * i;
-            if (j < num_bins && out->count[j] > mx) mx = out->count[j];
+            if (j < num_bins && count[j] > mx) mx = count[j];
         }
-        out->slot_max[i] = mx;
-        out->slot_off[i] = off;
-        off += mx * 32;
+        slot_max[i] = mx;
     }
-    out->w.assign(off, 0.f);
-    for (int i = 0; i < kMelSlots; ++i)
+    const int spec[kMelSlots] = {kMelSpec0, kMelSpec1, kMelSpec2, kMelSpec3};
+    bool fits = true;
+    for (int i = 0; i < kMelSlots; ++i) fits = fits && slot_max[i] <= spec[i];
+    if (fits)  // the unrolled path always runs its compile-time tap counts (weights are zero padded)
+        for (int i = 0; i < kMelSlots; ++i) slot_max[i] = spec[i];
+    for (int i = 0; i < kMelSlots; ++i) {
+        slot_off[i] = rows;
+        rows += slot_max[i];
+    }
+    *mel_spec = fits;
+    buf->assign(static_cast<size_t>(kTabMelW) + static_cast<size_t>(rows) * 32 + 3, 0.f);
+    buf->resize((buf->size() / 4) * 4);
+    float* b = buf->data();
+    // ---- window, transposed for 128-bit row reads ----
+    for (int n2 = 0; n2 < 16; ++n2)
+        for (int n1 = 0; n1 < 25; ++n1) b[kTabWin + kWinRow * n2 + n1] = 0.5f * window[16 * n1 + n2];
+    // ---- twiddles (double -> float) ----
+    const double two_pi = 2.0 * 3.14159265358979323846;
+    for (int t = 0; t < 16; ++t)
+        for (int n2 = 0; n2 < 16; ++n2) {
+            const double a = (t == 0) ? -two_pi * n2 / 32.0 : -two_pi * static_cast<double>((t * n2) % 512) / 512.0;
+            b[kTabTw + kExRowFloats * t + 2 * n2] = static_cast<float>(std::cos(a));
+            b[kTabTw + kExRowFloats * t + 2 * n2 + 1] = static_cast<float>(std::sin(a));
+        }
+    for (int n2 = 0; n2 < 16; ++n2) {
+        const double a = two_pi * n2 / 32.0;
+        b[kTabTwz + 2 * n2] = static_cast<float>(std::cos(a));
+        b[kTabTwz + 2 * n2 + 1] = static_cast<float>(std::sin(a));
+    }
+    // ---- mel: lane l, slot i owns mel bin l + 32 i ----
+    int* istart = reinterpret_cast<int*>(b + kTabMelStart);
+    int* ibin = reinterpret_cast<int*>(b + kTabMelBin);
+    int* info = reinterpret_cast<int*>(b + kTabMelInfo);
+    for (int i = 0; i < kMelSlots; ++i) {
+        info[i] = slot_max[i];
+        info[4 + i] = slot_off[i];
         for (int l = 0; l < 32; ++l) {
             const int j = l + 32 * i;
-            if (j >= num_bins) continue;
-            for (int r = 0; r < out->count[j]; ++r)
-                out->w[out->slot_off[i] + 32 * r + l] = dense[j * nb + out->start[j] + r];
+            ibin[32 * i + l] = j < num_bins ? j : -1;
+            int s0 = 0, shift = 0;
+            if (j < num_bins && count[j] > 0) {
+                s0 = start[j];
+                if (s0 + slot_max[i] > nb) {  // keep every tap inside the bins the kernel writes (0 .. nfft/2 - 1)
+                    shift = s0 + slot_max[i] - nb;
+                    s0 -= shift;
+                }
+                for (int r = 0; r < count[j]; ++r)
+                    b[kTabMelW + 32 * (slot_off[i] + shift + r) + l] = mel_dense[j * nb + start[j] + r];
+            }
+            istart[32 * i + l] = s0;
         }
+    }
     return true;
 }
 

@@ -5,7 +5,7 @@
 
 #include <vector>
 
-#include "fbank_tile.cuh"
+#include "fbank_stream.cuh"
 
 namespace psla {
 
@@ -14,18 +14,14 @@ namespace psla {
 void build_window_half(float* w, int n);
 // dense [num_bins][nfft/2] weights, kaldi.py:436-511 with vtln_warp == 1
 void build_mel_dense(float* mel, int num_bins, int nfft, float sample_rate, float low_freq, float high_freq);
-// TW[k1][n2] = exp(-2*pi*i*k1*n2/512) as (re, im) pairs, k1 < 32, n2 < 16
-void build_twiddles(float* tw);
-
-struct PackedMel {
-    short start[kMaxMel];
-    short count[kMaxMel];
-    int slot_max[kMelSlots];
-    int slot_off[kMelSlots];
-    std::vector<float> w;  // [sum slot_max][32]
-};
-// Returns false if the matrix cannot be represented (non-contiguous row support, a row wider than
-// kMelMaxCount, weight on bin >= nfft/2, num_bins > 128).
-bool pack_mel(const float* dense, int num_bins, int nfft, PackedMel* out);
+// The flat constant-table buffer the kernel copies into shared memory (layout: kTab* in fbank_stream.cuh):
+//   WINT[n2][28]  0.5 * window[16*n1 + n2]  (the 0.5 is the 1/2 of the two-real-FFTs-in-one separation)
+//   TW[t][n2]     t >= 1: exp(-2*pi*i*t*n2/512);  t == 0: exp(-2*pi*i*n2/32)   (re, im), row stride 36 floats
+//   TWZ[n2]       exp(+2*pi*i*n2/32)
+//   mel           per (slot, lane): first P bin, owned mel bin, zero-padded weights [tap][lane]
+// `window` is the analysis window itself [400]; `mel_dense` is [num_bins][nfft/2].
+// Returns false if the mel matrix cannot be represented (non-contiguous row support, a row wider than kMelMaxCount,
+// num_bins > 128).  *mel_spec is set when the tap counts fit the fully unrolled path (kMelSpec*).
+bool build_table_buffer(const float* window, const float* mel_dense, int num_bins, std::vector<float>* buf, bool* mel_spec);
 
 }  // namespace psla

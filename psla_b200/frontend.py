@@ -68,13 +68,14 @@ class GpuFbankFrontend:
     mean, std, skip_norm (optional).  freqm / timem / mixup are consumed by the host-side parameter draw
     (psla_b200.dataloaders), the kernel receives the drawn offsets.
 
+    exact_clip_mean: see psla_frontend_set_exact_clip_mean in include/psla_frontend.h.
     norm_std_scale: 1.0 reproduces this reference (`/ norm_std`, :192); 2.0 gives the `/ (norm_std * 2)`
     form of upstream PSLA/AST that BASELINE.json's north_star sentence quotes.
     """
 
     def __init__(self, audio_conf: dict, device: Union[int, str, torch.device, None] = None,
                  norm_std_scale: float = 1.0, fast_log: bool = True, tables_from: str = "torch",
-                 sample_rate: int = SAMPLE_RATE):
+                 sample_rate: int = SAMPLE_RATE, exact_clip_mean: bool = False):
         if not torch.cuda.is_available():
             raise RuntimeError("GpuFbankFrontend needs a CUDA device; psla_b200 has no CPU path")
         self.lib = _lib.load()
@@ -107,6 +108,7 @@ class GpuFbankFrontend:
         elif tables_from != "native":
             raise ValueError("tables_from must be 'torch' or 'native'")
         self.set_fast_log(fast_log)
+        self.set_exact_clip_mean(exact_clip_mean)
         self._ws = {}
 
     # ---- lifetime ----
@@ -125,6 +127,12 @@ class GpuFbankFrontend:
     def set_fast_log(self, enable: bool):
         self.fast_log = bool(enable)
         _lib.check(self.lib.psla_frontend_set_fast_log(self._h, int(self.fast_log)), "set_fast_log", self._h)
+
+    def set_exact_clip_mean(self, enable: bool):
+        """False (default): the whole-clip DC removal is folded into the per-frame one (no pass over the clip);
+        True: clip means from a statistics kernel, the reference's fp32 expression verbatim."""
+        self.exact_clip_mean = bool(enable)
+        _lib.check(self.lib.psla_frontend_set_exact_clip_mean(self._h, int(self.exact_clip_mean)), "set_exact_clip_mean", self._h)
 
     def set_timing(self, enable: bool):
         _lib.check(self.lib.psla_frontend_set_timing(self._h, int(bool(enable))), "set_timing", self._h)

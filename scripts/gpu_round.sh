@@ -17,6 +17,6 @@ $SHORT > gpurun_out/plain.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $SHORT > gpurun_out/ncu_list.log 2>&1
 echo "ncu list rc=$?"
 $SHORT > gpurun_out/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:fbank_tile -s 4 -c 2 -f -o gpurun_out/prof_tile $SHORT > gpurun_out/ncu_full.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:fbank_stream -s 3 -c 2 -f -o gpurun_out/prof_stream $SHORT > gpurun_out/ncu_full.log 2>&1
 echo "ncu full rc=$?"
 ls -la gpurun_out

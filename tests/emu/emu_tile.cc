@@ -1,15 +1,14 @@
-// CPU lane-stepping harness for the sm_100a tile kernel (TEST ONLY, built by tests/test_emu.py with g++).
+// CPU lane-stepping harness for the sm_100a streaming kernel (TEST ONLY, built by tests/test_emu.py with g++).
 //
-// It runs the very same per-lane functions the CUDA kernel calls (psla_b200/csrc/fbank_tile.cuh),
-// one simulated lane after another with the __syncwarp points turned into loop boundaries, on a
-// staged tile built by plain scalar code.  It checks index maps / twiddles / the two-pass FFT /
-// the separation / the sparse mel layout without a GPU.  It is not a fallback: nothing in
-// psla_b200 can load it.
+// It runs the very same per-lane functions the CUDA kernel calls (psla_b200/csrc/fbank_stream.cuh), one simulated
+// lane after another with the __syncwarp points turned into loop boundaries, on a staged group window built by plain
+// scalar code.  It checks index maps / twiddles / the two-pass FFT / the separation / the sparse mel layout / the
+// table buffer without a GPU.  It is not a fallback: nothing in psla_b200 can load it.
 #include <cmath>
 #include <cstring>
 #include <vector>
 
-#include "../../psla_b200/csrc/fbank_tile.cuh"
+#include "../../psla_b200/csrc/fbank_stream.cuh"
 #include "../../psla_b200/csrc/tables.h"
 
 using namespace psla;
@@ -17,38 +16,48 @@ using namespace psla;
 extern "C" {
 
 // x: mean-removed (and mixed) waveform, n samples.  out: [m][num_bins] raw log-mel (floor applied).
-// mel_dense: optional [num_bins][256] override (nullptr = native table).  window_half likewise.
-int emu_fbank(const float* x, int n, int num_bins, const float* mel_dense, const float* window_half, float* out) {
+// mel_dense: optional [num_bins][256] override (nullptr = native table); window: optional [400] analysis window.
+// force_generic_mel != 0 runs the run-time-loop mel path even when the unrolled one applies.
+int emu_fbank(const float* x, int n, int num_bins, const float* mel_dense, const float* window, int force_generic_mel,
+              float* out) {
     if (n < kFrameLen) return -1;
     const int m = 1 + (n - kFrameLen) / kFrameShift;
-    std::vector<float> win(kFrameLen), tw(32 * 16 * 2), dense(num_bins * 256);
-    if (window_half) std::memcpy(win.data(), window_half, sizeof(float) * kFrameLen);
-    else build_window_half(win.data(), kFrameLen);
+    std::vector<float> win(kFrameLen), dense(num_bins * 256);
+    if (window) std::memcpy(win.data(), window, sizeof(float) * kFrameLen);
+    else {
+        build_window_half(win.data(), kFrameLen);
+        for (auto& v : win) v *= 2.f;
+    }
     if (mel_dense) std::memcpy(dense.data(), mel_dense, sizeof(float) * num_bins * 256);
     else build_mel_dense(dense.data(), num_bins, kNfft, 16000.f, 20.f, 0.f);
-    build_twiddles(tw.data());
-    PackedMel pm;
-    if (!pack_mel(dense.data(), num_bins, kNfft, &pm)) return -2;
-    MelTableView mt{pm.start, pm.count, pm.slot_max, pm.slot_off, pm.w.data()};
+    std::vector<float> tab;
+    bool spec = false;
+    if (!build_table_buffer(win.data(), dense.data(), num_bins, &tab, &spec)) return -2;
+    if (force_generic_mel) spec = false;
+    const float* TAB = tab.data();
+    MelView mt{reinterpret_cast<const int*>(TAB + kTabMelStart), reinterpret_cast<const int*>(TAB + kTabMelBin),
+               reinterpret_cast<const int*>(TAB + kTabMelInfo), TAB + kTabMelW};
 
     const float p = 0.97f;
     const float c1 = static_cast<float>(1.0 - static_cast<double>(p));
     const float eps = 1.1920928955078125e-07f;
-    std::vector<float> D(kStageFloats), XS(kFramesPerCta + 2), BS(kBlk16PerTile + 1);
-    std::vector<float> EXw(2 * kExPairFloats);
+    std::vector<float> W(kWarpFloats, 0.f);
+    float* D = W.data() + kWsD;
+    float* BS = W.data() + kWsBS;
+    float* XS = W.data() + kWsXS;
+    float* EX = W.data() + kWsEX;
 
-    for (int F0 = 0; F0 < m; F0 += kFramesPerCta) {
-        const int S0 = F0 * kFrameShift;
-        // ---- staging (scalar restatement of the kernel's cooperative load) ----
-        std::fill(D.begin(), D.end(), 0.f);
-        for (int u = 0; u < kTileSamples; ++u) {
+    for (int f0 = 0; f0 < m; f0 += kGroupFrames) {
+        const int S0 = f0 * kFrameShift;
+        // ---- staging (scalar restatement of the kernel's warp-private staging) ----
+        for (int u = 0; u < kGroupSamples; ++u) {
             const int s = S0 + u;
             const float xc = s < n ? x[s] : 0.f;
             const float xp = (u > 0 && s - 1 < n) ? x[s - 1] : 0.f;
             D[dpad(u)] = fmaf(-p, xp, xc);
-            if (u % kFrameShift == 0 && u / kFrameShift < kFramesPerCta) XS[u / kFrameShift] = c1 * xc;
+            if (u % kFrameShift == 0) XS[u / kFrameShift] = c1 * xc;
         }
-        for (int q = 0; q < kBlk16PerTile; ++q) {
+        for (int q = 0; q < kGroupSamples / 16; ++q) {
             // same association as the kernel: 4 x (sum of 4) combined by two xor-shuffle steps
             float s4[4];
             for (int g = 0; g < 4; ++g) {
@@ -59,58 +68,80 @@ int emu_fbank(const float* x, int n, int num_bins, const float* mel_dense, const
             }
             BS[q] = (s4[0] + s4[1]) + (s4[2] + s4[3]);
         }
-        for (int w = 0; w < kWarpsPerCta; ++w) {
-            float cmu[4];
-            for (int q = 0; q < 4; ++q) {
-                const int lf = 4 * w + q;
-                float sum = 0.f;
-                for (int k = 0; k < 25; ++k) sum += BS[10 * lf + k];
-                cmu[q] = c1 * (sum * (1.0f / kFrameLen));
+        // ---- per-frame means: lane 8 f + j adds blocks 10 f + j (+8, +16, and +24 for j == 0), xor tree over j ----
+        float cmu[4];
+        for (int f = 0; f < 4; ++f) {
+            float part[8];
+            for (int j = 0; j < 8; ++j) {
+                float a = (BS[10 * f + j] + BS[10 * f + j + 8]) + BS[10 * f + j + 16];
+                if (j == 0) a += BS[10 * f + 24];
+                part[j] = a;
             }
-            float* P = EXw.data();
-            float regs[32][4][16];
-            for (int lane = 0; lane < 32; ++lane) {  // pass 1
-                const int h = lane >> 4, n2 = lane & 15;
-                pair_pass1(n2, 4 * w + 2 * h, D.data(), XS.data(), win.data(), tw.data(), EXw.data() + h * kExPairFloats,
-                           cmu[2 * h], cmu[2 * h + 1]);
+            for (int o = 1; o < 8; o <<= 1) {
+                float nxt[8];
+                for (int j = 0; j < 8; ++j) nxt[j] = part[j] + part[j ^ o];
+                std::memcpy(part, nxt, sizeof(part));
             }
-            for (int lane = 0; lane < 32; ++lane) {  // pass 2a (reads)   -- __syncwarp --
-                const int h = lane >> 4, t = lane & 15;
-                pair_pass2_fft(t, EXw.data() + h * kExPairFloats, regs[lane][0], regs[lane][1], regs[lane][2], regs[lane][3]);
-            }
-            for (int lane = 0; lane < 32; ++lane) {  // pass 2b (P aliases EX) -- __syncwarp --
-                const int h = lane >> 4, t = lane & 15;
-                pair_power_store(t, regs[lane][0], regs[lane][1], regs[lane][2], regs[lane][3], P + (2 * h) * kPRowFloats,
-                                 P + (2 * h + 1) * kPRowFloats);
-            }
-            for (int lane = 0; lane < 32; ++lane) {  // mel                    -- __syncwarp --
-                float acc[kMelSlots][kFramesPerWarp];
-                warp_mel(lane, P, mt, acc);
-                for (int i = 0; i < kMelSlots; ++i)
-                    for (int f = 0; f < kFramesPerWarp; ++f) {
-                        const int row = F0 + 4 * w + f, j = lane + 32 * i;
-                        if (row < m && j < num_bins) out[row * num_bins + j] = logf(fmaxf(acc[i][f], eps));
-                    }
-            }
+            cmu[f] = c1 * (part[0] * (1.0f / kFrameLen));
+        }
+        float regs[32][4][16];
+        for (int lane = 0; lane < 32; ++lane) {  // pass 1
+            const int h = lane >> 4, n2 = lane & 15;
+            pair_pass1(n2, h, D, XS, TAB + kTabWin, TAB + kTabTwz, EX + h * kExPairFloats, cmu[2 * h], cmu[2 * h + 1]);
+        }
+        for (int lane = 0; lane < 32; ++lane) {  // pass 2a (reads)   -- __syncwarp --
+            const int h = lane >> 4, t = lane & 15;
+            pair_pass2_fft(t, EX + h * kExPairFloats, TAB + kTabTw, regs[lane][0], regs[lane][1], regs[lane][2], regs[lane][3]);
+        }
+        for (int lane = 0; lane < 32; ++lane) {  // pass 2b (P aliases EX) -- __syncwarp --
+            const int h = lane >> 4, t = lane & 15;
+            pair_power_store(t, h, regs[lane][0], regs[lane][1], regs[lane][2], regs[lane][3], EX);
+        }
+        for (int lane = 0; lane < 32; ++lane) {  // mel                    -- __syncwarp --
+            float acc[kMelSlots][kGroupFrames];
+            if (spec) warp_mel<true>(lane, EX, mt, acc);
+            else warp_mel<false>(lane, EX, mt, acc);
+            for (int i = 0; i < kMelSlots; ++i)
+                for (int f = 0; f < kGroupFrames; ++f) {
+                    const int row = f0 + f, j = mt.bin[32 * i + lane];
+                    if (row < m && j >= 0) out[row * num_bins + j] = logf(fmaxf(acc[i][f], eps));
+                }
         }
     }
     return m;
 }
 
-// expose the native tables for table-parity tests
-void emu_tables(int num_bins, float* window_half, float* mel_dense, float* tw) {
-    build_window_half(window_half, kFrameLen);
+// expose the native tables for table-parity tests: window [400] (not halved), dense mel, and the flat table buffer
+int emu_tables(int num_bins, float* window, float* mel_dense, float* tab, int tab_cap, int* mel_spec) {
+    build_window_half(window, kFrameLen);
+    for (int j = 0; j < kFrameLen; ++j) window[j] *= 2.f;
     build_mel_dense(mel_dense, num_bins, kNfft, 16000.f, 20.f, 0.f);
-    build_twiddles(tw);
+    std::vector<float> buf;
+    bool spec = false;
+    if (!build_table_buffer(window, mel_dense, num_bins, &buf, &spec)) return -1;
+    *mel_spec = spec ? 1 : 0;
+    if (static_cast<int>(buf.size()) > tab_cap) return -2;
+    std::memcpy(tab, buf.data(), buf.size() * sizeof(float));
+    return static_cast<int>(buf.size());
 }
 
-// raw 512-point complex FFT through pass1/pass2 machinery is covered by emu_fbank; this one checks
-// the register FFT templates alone against a direct DFT (N = 16 and 32).
+// table offsets (floats) so the test can slice the buffer: win, tw, twz, mel_start, mel_bin, mel_info, mel_w, row strides
+void emu_layout(int* v) {
+    v[0] = kTabWin; v[1] = kTabTw; v[2] = kTabTwz; v[3] = kTabMelStart; v[4] = kTabMelBin; v[5] = kTabMelInfo;
+    v[6] = kTabMelW; v[7] = kWinRow; v[8] = kExRowFloats;
+}
+
+// the register FFT templates alone against a direct DFT (N = 16, 32) and the pruned 32-point variant (n = -32:
+// inputs 25..31 are ignored / treated as zero)
 void emu_fft(int n, const float* in_re, const float* in_im, float* out_re, float* out_im) {
-    if (n == 32) {
+    if (n == 32 || n == -32) {
         float re[32], im[32];
         for (int i = 0; i < 32; ++i) { re[i] = in_re[i]; im[i] = in_im[i]; }
-        fft_dif<32>(re, im);
+        if (n == 32) fft_dif<32>(re, im);
+        else {
+            for (int i = 25; i < 32; ++i) re[i] = im[i] = 0.f;
+            fft32_zero_tail(re, im);
+        }
         for (int r = 0; r < 32; ++r) { out_re[brev<5>(r)] = re[r]; out_im[brev<5>(r)] = im[r]; }
     } else {
         float re[16], im[16];

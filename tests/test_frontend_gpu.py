@@ -40,9 +40,30 @@ def FE():
     return GpuFbankFrontend
 
 
-@pytest.fixture(scope="module")
-def fe(FE):
-    return FE(CONF)
+@pytest.fixture(scope="module", params=[False, True], ids=["fused-mean", "exact-mean"])
+def fe(FE, request):
+    """Both treatments of the whole-clip DC removal (include/psla_frontend.h: psla_frontend_set_exact_clip_mean)."""
+    return FE(CONF, exact_clip_mean=request.param)
+
+
+def _same_fill_cells(out, ref, fill, div=STD, tol=TOL):
+    """Masked / padded cells hold the same fp32 constant in both.  A LIVE cell may round to that constant by chance in
+    one of the two (seen: 1 cell in 13.5 M); such a cell must still agree within the tolerance."""
+    a, b = out == fill, ref == fill
+    mism = a ^ b
+    assert mism.sum().item() <= max(1, int(2e-7 * out.numel()))
+    if mism.any():
+        assert ((out - ref).abs()[mism] * div).max().item() <= tol
+
+
+def _dead_cells(lengths, masks, T, F=128):
+    """Cells the reference fills with 0.0 before normalisation: padding rows, time-mask rows, frequency-mask columns."""
+    dead = torch.zeros(len(lengths), T, F, dtype=torch.bool)
+    for b, (n, (f0, fw, t0, tw)) in enumerate(zip(lengths, masks)):
+        dead[b, min(O.num_frames(n), T):] = True
+        dead[b, t0:t0 + tw] = True
+        dead[b, :, f0:f0 + fw] = True
+    return dead
 
 
 def _check(out, ref, div=STD, tol=TOL, fill=None):
@@ -50,7 +71,7 @@ def _check(out, ref, div=STD, tol=TOL, fill=None):
     assert out.shape == ref.shape and out.dtype == torch.float32
     assert not torch.isnan(out).any()
     if fill is not None:  # mask placement and padding: same cells, same fp32 constant
-        assert torch.equal(out == fill, ref == fill)
+        _same_fill_cells(out, ref, fill, div, tol)
     err = ((out - ref).abs() * div).max().item()
     assert err <= tol, err
     return err
@@ -216,7 +237,9 @@ def test_c2_audioset_train_batch(fe):
     ref = O.batch_torch(waves, src1, src2, lam, masks, 1056, MEAN, STD)
     ref64 = O.batch_torch(waves, src1, src2, lam, masks, 1056, MEAN, STD, dtype=torch.float64)
     fill = _fill()
-    assert torch.equal(out == fill, ref == fill)  # bit-exact mask / pad placement
+    dead = _dead_cells([160000] * B, masks, 1056)  # bit-exact mask / pad placement
+    assert (out[dead] == fill).all() and (ref[dead] == fill).all()
+    _same_fill_cells(out, ref, fill)
     err = (out - ref).abs() * STD
     ours64 = (out.double() - ref64).abs() * STD
     ref_err = (ref.double() - ref64).abs() * STD  # the fp32 reference's own distance to fp64 truth

@@ -84,9 +84,13 @@ constexpr int kXsFloats = 8;   // (1-p) * x at u = 0, 160, ..., 800
 // (LDS.128, one row per lane) are bank-conflict free.
 constexpr int kExRowFloats = 36;
 constexpr int kExPairFloats = 32 * kExRowFloats;  // 1152 floats = 4608 B
+// Pass 2 interleaves the two pairs over the lanes (lane = 2 t + h, so that a lane pair stores the 4 frames of a bin as
+// one contiguous 16 bytes); the second pair's buffer starts 16 floats later so that (t, 0) and (t, 1) hit different banks.
+constexpr int kExSecondPair = kExPairFloats + 16;
+constexpr int kExFloats = kExSecondPair + kExPairFloats;  // 2320
 // Power spectra of the warp's 4 frames, P[bin][frame], alias the exchange buffers once pass 2 has read them.
 constexpr int kPFloats = 4 * (kNfft / 2);  // bins 0..255 (bin 256 never carries mel weight: kaldi.py:627 pads a zero column)
-static_assert(kPFloats <= 2 * kExPairFloats, "P must fit in the warp's exchange buffers");
+static_assert(kPFloats <= kExFloats, "P must fit in the warp's exchange buffers");
 
 // per-warp shared-memory window (floats)
 constexpr int kWsD = 0;
@@ -95,7 +99,7 @@ constexpr int kWsXS = kWsBS + kBsFloats;
 constexpr int kWsCS = kWsXS + kXsFloats;  // per-clip state of the warp (kept out of the register file, see stream_kernel.cuh)
 constexpr int kCsWords = 24;
 constexpr int kWsEX = kWsCS + kCsWords;
-constexpr int kWarpFloats = kWsEX + 2 * kExPairFloats;  // 3304 floats = 13216 B
+constexpr int kWarpFloats = kWsEX + kExFloats;  // 3320 floats = 13280 B
 static_assert((kWsEX * 4) % 16 == 0 && (kWarpFloats * 4) % 16 == 0, "16-byte alignment of vector regions");
 
 // Constant tables (floats), copied once per CTA into shared memory.

@@ -509,15 +509,16 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
         cmu_x = __shfl_sync(0xffffffffu, cmu, 16 * h);
         cmu_y = __shfl_sync(0xffffffffu, cmu, 16 * h + 8);
     }
-    float* EXp = EX + h * kExPairFloats;
-    pair_pass1(n2, h, D, XS, TAB + kTabWin, TAB + kTabTwz, EXp, cmu_x, cmu_y);
+    pair_pass1(n2, h, D, XS, TAB + kTabWin, TAB + kTabTwz, EX + h * kExSecondPair, cmu_x, cmu_y);
     __syncwarp();
     if (next_live) stage_shift(lane, D, BS, XS);
     {
+        // pass 2 re-maps the lanes: pair h2 = lane & 1, row t = lane >> 1 (see kExSecondPair)
+        const int h2 = lane & 1, t = lane >> 1;
         float ar[16], ai[16], br[16], bi[16];
-        pair_pass2_fft(n2, EXp, TAB + kTabTw, ar, ai, br, bi);
+        pair_pass2_fft(t, EX + h2 * kExSecondPair, TAB + kTabTw, ar, ai, br, bi);
         __syncwarp();  // P aliases EX: all reads done before any write
-        pair_power_store(n2, h, ar, ai, br, bi, EX);
+        pair_power_store(t, h2, ar, ai, br, bi, EX);
     }
     __syncwarp();
     constexpr int NIT = StageGeom<kOverlapSamples>::kIters;

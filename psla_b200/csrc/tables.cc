@@ -104,23 +104,94 @@ bool build_table_buffer(const float* window, const float* mel_dense, int num_bin
         b[kTabTwz + 2 * n2] = static_cast<float>(std::cos(a));
         b[kTabTwz + 2 * n2 + 1] = static_cast<float>(std::sin(a));
     }
-    // ---- mel: lane l, slot i owns mel bin l + 32 i ----
+    // ---- mel: slot i owns mel bins 32 i .. 32 i + 31, one per lane ----
+    // A tap is one 128-bit shared-memory read of P[bin][4 frames]; the 8 lanes of a quarter-warp are served together
+    // and collide when their bins differ but are congruent mod 8.  Two freedoms remove the collisions: WHICH lane of
+    // the slot owns a mel bin (the output row is one 128-byte line either way), and WHERE a row's taps start (rows
+    // narrower than the slot's tap count can begin earlier, on zero weights).  Rows pick a start residue mod 8 such
+    // that every residue is used at most 4 times (bipartite matching, capacity 4), then each quarter-warp takes one
+    // row of every residue.
     int* istart = reinterpret_cast<int*>(b + kTabMelStart);
     int* ibin = reinterpret_cast<int*>(b + kTabMelBin);
     int* info = reinterpret_cast<int*>(b + kTabMelInfo);
     for (int i = 0; i < kMelSlots; ++i) {
         info[i] = slot_max[i];
         info[4 + i] = slot_off[i];
+        const int R = slot_max[i];
+        int nrows = 0, rows_j[32], lo_start[32], hi_start[32];  // allowed starts of a row: [lo_start, hi_start]
         for (int l = 0; l < 32; ++l) {
             const int j = l + 32 * i;
-            ibin[32 * i + l] = j < num_bins ? j : -1;
-            int s0 = 0, shift = 0;
-            if (j < num_bins && count[j] > 0) {
-                s0 = start[j];
-                if (s0 + slot_max[i] > nb) {  // keep every tap inside the bins the kernel writes (0 .. nfft/2 - 1)
-                    shift = s0 + slot_max[i] - nb;
-                    s0 -= shift;
+            if (j >= num_bins) break;
+            rows_j[nrows] = j;
+            if (count[j] == 0) {  // empty row: all weights zero, any start inside the spectrum
+                lo_start[nrows] = 0;
+                hi_start[nrows] = R > 0 ? (nb - R < 7 ? nb - R : 7) : 0;
+            } else {
+                int hi = start[j], lo = start[j] - (R - count[j]);
+                if (hi + R > nb) hi = nb - R;  // keep every tap inside the bins the kernel writes (0 .. nfft/2 - 1)
+                if (lo < 0) lo = 0;
+                lo_start[nrows] = lo;
+                hi_start[nrows] = hi;
+            }
+            ++nrows;
+        }
+        // residue -> rows matching (capacity 4 per residue)
+        int owner[8][4], used[8] = {0}, res_of[32];
+        for (int r = 0; r < 8; ++r)
+            for (int c = 0; c < 4; ++c) owner[r][c] = -1;
+        for (int n = 0; n < nrows; ++n) res_of[n] = -1;
+        auto allowed = [&](int n, int r) {  // some start in [lo, hi] congruent to r mod 8?
+            const int first = lo_start[n] + ((r - lo_start[n]) % 8 + 8) % 8;
+            return first <= hi_start[n];
+        };
+        bool seen[8];
+        auto try_assign = [&](auto&& self, int n) -> bool {
+            for (int r = 0; r < 8; ++r) {
+                if (seen[r] || !allowed(n, r)) continue;
+                seen[r] = true;
+                if (used[r] < 4) {
+                    owner[r][used[r]++] = n;
+                    res_of[n] = r;
+                    return true;
                 }
+                for (int c = 0; c < 4; ++c) {
+                    const int other = owner[r][c];
+                    if (self(self, other)) {
+                        owner[r][c] = n;
+                        res_of[n] = r;
+                        return true;
+                    }
+                }
+            }
+            return false;
+        };
+        bool perfect = true;
+        for (int n = 0; n < nrows; ++n) {
+            for (bool& v : seen) v = false;
+            if (!try_assign(try_assign, n)) perfect = false;
+        }
+        // lanes: quarter-warp q takes the q-th row of every residue; rows left without a residue fill the gaps
+        int lane_row[32];
+        for (int l = 0; l < 32; ++l) lane_row[l] = -1;
+        if (perfect) {
+            int fill_q[4] = {0, 0, 0, 0};
+            for (int r = 0; r < 8; ++r)
+                for (int c = 0; c < used[r]; ++c) lane_row[8 * c + fill_q[c]++] = owner[r][c];
+        } else {  // could not avoid every collision: keep the natural order and the latest starts
+            for (int n = 0; n < nrows; ++n) {
+                lane_row[n] = n;
+                res_of[n] = -1;
+            }
+        }
+        for (int l = 0; l < 32; ++l) {
+            const int n = lane_row[l];
+            ibin[32 * i + l] = n >= 0 ? rows_j[n] : -1;
+            int s0 = 0;
+            if (n >= 0) {
+                const int j = rows_j[n];
+                s0 = hi_start[n];
+                if (res_of[n] >= 0) s0 -= ((hi_start[n] - res_of[n]) % 8 + 8) % 8;  // latest allowed start with that residue
+                const int shift = count[j] > 0 ? start[j] - s0 : 0;
                 for (int r = 0; r < count[j]; ++r)
                     b[kTabMelW + 32 * (slot_off[i] + shift + r) + l] = mel_dense[j * nb + start[j] + r];
             }

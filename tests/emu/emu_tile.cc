@@ -87,14 +87,14 @@ int emu_fbank(const float* x, int n, int num_bins, const float* mel_dense, const
         float regs[32][4][16];
         for (int lane = 0; lane < 32; ++lane) {  // pass 1
             const int h = lane >> 4, n2 = lane & 15;
-            pair_pass1(n2, h, D, XS, TAB + kTabWin, TAB + kTabTwz, EX + h * kExPairFloats, cmu[2 * h], cmu[2 * h + 1]);
+            pair_pass1(n2, h, D, XS, TAB + kTabWin, TAB + kTabTwz, EX + h * kExSecondPair, cmu[2 * h], cmu[2 * h + 1]);
         }
         for (int lane = 0; lane < 32; ++lane) {  // pass 2a (reads)   -- __syncwarp --
-            const int h = lane >> 4, t = lane & 15;
-            pair_pass2_fft(t, EX + h * kExPairFloats, TAB + kTabTw, regs[lane][0], regs[lane][1], regs[lane][2], regs[lane][3]);
+            const int h = lane & 1, t = lane >> 1;
+            pair_pass2_fft(t, EX + h * kExSecondPair, TAB + kTabTw, regs[lane][0], regs[lane][1], regs[lane][2], regs[lane][3]);
         }
         for (int lane = 0; lane < 32; ++lane) {  // pass 2b (P aliases EX) -- __syncwarp --
-            const int h = lane >> 4, t = lane & 15;
+            const int h = lane & 1, t = lane >> 1;
             pair_power_store(t, h, regs[lane][0], regs[lane][1], regs[lane][2], regs[lane][3], EX);
         }
         for (int lane = 0; lane < 32; ++lane) {  // mel                    -- __syncwarp --

@@ -83,8 +83,11 @@ def test_native_tables_vs_torch_order_tables(emu, golden_dir):
     w = tab[o_mw:].reshape(-1, 32)[:info[:4].sum()]
     dense = np.zeros_like(mel)
     for i in range(4):
+        assert sorted(mbin[i]) == list(range(32 * i, 32 * i + 32))  # a permutation inside the slot: one 128 B output line
+        for q in range(4):  # the 8 lanes of a quarter-warp read 8 different bank groups (or the same bin)
+            st = start[i, 8 * q:8 * q + 8]
+            assert all(st[a] == st[c] or st[a] % 8 != st[c] % 8 for a in range(8) for c in range(a))
         for l in range(32):
-            assert mbin[i, l] == l + 32 * i
             for r in range(info[i]):
                 k = start[i, l] + r
                 assert 0 <= k < 256

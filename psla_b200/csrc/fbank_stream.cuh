@@ -12,12 +12,12 @@
 // (32 complex values = 64 registers per lane):
 //   pass 1   lane n2 (0..15) holds z[16*n1 + n2], n1 = 0..31 (only n1 < 25 is non-zero: 400 = 25*16).  The y frame
 //            starts 160 samples = 10 n1-steps after the x frame, so ONE run of 35 staged values feeds both.
-//            -> 32-point DIF FFT over n1 in registers (first stage pruned for the 7 zero inputs) -> shared memory
+//            -> 32-point DIT FFT over n1 in registers (FMA-only butterflies, first stage pruned for the 7 zero inputs) -> shared memory
 //            EX[k1][n2], untwiddled (row 0 pre-multiplied by W_32^-n2, see below).
 //   pass 2   lane t reads rows ka = t and kb = 32 - t (lane 0: rows 0 and 16), multiplies row ka by
 //            TW[t][n2] = W_512^(t*n2) and row kb by conj(TW[t][n2]): because W_512^((32-t)*n2) = W_16^n2 * conj(TW[t][n2])
 //            and a modulation by W_16^n2 only rotates the 16-point FFT's output index by one, both rows share one
-//            table row.  Two 16-point DIF FFTs over n2 in registers.  Z[k] and Z[512-k] are then in the SAME lane, so
+//            table row.  Two 16-point DIT FFTs over n2 in registers.  Z[k] and Z[512-k] are then in the SAME lane, so
 //            the two real spectra separate without any exchange (the 1/2 is folded into the window table); the power
 //            spectra go to shared memory as P[bin][frame 0..3].
 //            Lane 0's table row is W_32^n2 (what row 16 needs after conj + rotation); pass 1 compensates row 0.
@@ -97,9 +97,9 @@ constexpr int kWsD = 0;
 constexpr int kWsBS = kWsD + kDFloats;
 constexpr int kWsXS = kWsBS + kBsFloats;
 constexpr int kWsCS = kWsXS + kXsFloats;  // per-clip state of the warp (kept out of the register file, see stream_kernel.cuh)
-constexpr int kCsWords = 24;
+constexpr int kCsWords = 28;
 constexpr int kWsEX = kWsCS + kCsWords;
-constexpr int kWarpFloats = kWsEX + kExFloats;  // 3320 floats = 13280 B
+constexpr int kWarpFloats = kWsEX + kExFloats;  // 3324 floats = 13296 B
 static_assert((kWsEX * 4) % 16 == 0 && (kWarpFloats * 4) % 16 == 0, "16-byte alignment of vector regions");
 
 // Constant tables (floats), copied once per CTA into shared memory.
@@ -117,31 +117,6 @@ constexpr int kMelSlots = 4;
 constexpr int kMelMaxCount = 128;  // per-row tap bound of the generic path (the table must also fit in shared memory)
 // tap counts the specialised (fully unrolled) mel path is compiled for: 16 kHz / 128 bins needs (2, 3, 6, 10)
 constexpr int kMelSpec0 = 2, kMelSpec1 = 3, kMelSpec2 = 6, kMelSpec3 = 10;
-
-// ---------------------------------------------------------------------------------------------
-// 32-point DIF FFT whose inputs n1 >= 25 are zero: the first stage pairs (j, j+16); for j >= 9 the upper input is
-// zero, so the butterfly degenerates to (u, u * W_32^j) -- no additions.
-// ---------------------------------------------------------------------------------------------
-PSLA_HD void fft32_zero_tail(float (&re)[32], float (&im)[32]) {
-    static_for<0, 16>([&](auto j_) {
-        constexpr int j = decltype(j_)::value;
-        if constexpr (j + 16 < 25) {
-            const float ur = re[j], ui = im[j], vr = re[j + 16], vi = im[j + 16];
-            re[j] = ur + vr;
-            im[j] = ui + vi;
-            float dr = ur - vr, di = ui - vi;
-            mul_twiddle<j, 32>(dr, di);
-            re[j + 16] = dr;
-            im[j + 16] = di;
-        } else {
-            float dr = re[j], di = im[j];
-            mul_twiddle<j, 32>(dr, di);
-            re[j + 16] = dr;
-            im[j + 16] = di;
-        }
-    });
-    fft_dif<32, 16>(re, im);
-}
 
 // ---------------------------------------------------------------------------------------------
 // Pass 1 of half-warp h, lane n2: frames 2h (x) and 2h+1 (y) of the group.
@@ -177,7 +152,7 @@ PSLA_HD void pair_pass1(int n2, int h, const float* __restrict__ D, const float*
             im[n1] = ((n1 == 0 ? vy0 : v[n1 + 10]) - cmu_y) * w[n1];
         });
     }
-    fft32_zero_tail(re, im);
+    fft_dit<32, 5, 25>(re, im);  // inputs n1 >= 25 are zero (400 = 25 * 16)
     float zr, zi;
     ld2(TWZ + 2 * n2, zr, zi);
     static_for<0, 32>([&](auto r_) {
@@ -194,7 +169,7 @@ PSLA_HD void pair_pass1(int n2, int h, const float* __restrict__ D, const float*
 }
 
 // ---------------------------------------------------------------------------------------------
-// Pass 2a of lane t: rows ka / kb times TW[t] / conj(TW[t]), two 16-point DIF FFTs.
+// Pass 2a of lane t: rows ka / kb times TW[t] / conj(TW[t]), two 16-point DIT FFTs.
 //   a[brev4(k2)]            = Z[ka + 32*k2]
 //   b[brev4((k2 + 1) % 16)] = Z[kb + 32*k2]      (the W_16^n2 modulation rotates the output index)
 // ---------------------------------------------------------------------------------------------
@@ -229,8 +204,8 @@ PSLA_HD void pair_pass2_fft(int t, const float* __restrict__ EX, const float* __
         bi[n + 1] = bi[n + 1] * w1r - br[n + 1] * w1i;
         br[n + 1] = yr;
     });
-    fft_dif<16>(ar, ai);
-    fft_dif<16>(br, bi);
+    fft_dit<16, 4>(ar, ai);
+    fft_dit<16, 4>(br, bi);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -1,4 +1,4 @@
-// In-register radix-2 DIF FFTs with compile-time twiddles.
+// In-register radix-2 DIT FFTs with compile-time twiddles.
 //
 // Everything here is `__host__ __device__` so that the exact per-thread code the sm_100a kernel
 // runs can also be compiled by g++ and stepped "one simulated lane at a time" by the CPU test
@@ -78,61 +78,78 @@ struct Twiddle {
     static constexpr float im = static_cast<float>(-ct_sin2pi(K, N));
 };
 
-// (ar + i ai) *= W_N^K with the trivial cases folded away
-template <int K, int N>
-PSLA_HD void mul_twiddle(float& ar, float& ai) {
-    constexpr int k = ((K % N) + N) % N;
-    if constexpr (k == 0) {
-    } else if constexpr (4 * k == N) {  // -i
-        float t = ar;
-        ar = ai;
-        ai = -t;
-    } else if constexpr (2 * k == N) {  // -1
-        ar = -ar;
-        ai = -ai;
-    } else if constexpr (4 * k == 3 * N) {  // +i
-        float t = ar;
-        ar = -ai;
-        ai = t;
-    } else if constexpr (8 * k == N) {  // (1 - i)/sqrt2
-        constexpr float h = Twiddle<1, 8>::re;
-        float t = (ar + ai) * h;
-        ai = (ai - ar) * h;
-        ar = t;
-    } else if constexpr (8 * k == 3 * N) {  // (-1 - i)/sqrt2
-        constexpr float h = Twiddle<1, 8>::re;
-        float t = (ai - ar) * h;
-        ai = -(ar + ai) * h;
-        ar = t;
+// ---------------------------------------------------------------------------------------------
+// Decimation-in-time FFT with FMA-only butterflies (Linzer-Feig): for a twiddle W = c + i*s
+//   |c| >= |s|:  W*b = c * (b_r - t*b_i,  b_i + t*b_r),  t = s/c      (2 FMA)   then  a +- c*(...)   (4 FMA)
+//   |c| <  |s|:  W*b = s * (t*b_r - b_i,  t*b_i + b_r),  t = c/s
+// i.e. 6 instructions per non-trivial butterfly instead of the 8 of the multiply-after-subtract DIF form, and 4 for
+// W in {1, -i}.  Natural-order input, bit-reversed output: X[brev(r)] = (re[r], im[r]) -- the DIT network runs
+// on the bit-reversed view y[i] = x[brev(i)], so "in place" it leaves X[k] at index brev(k).
+// NZ: inputs with index >= NZ are known to be zero (their first-stage butterflies become copies).
+// ---------------------------------------------------------------------------------------------
+template <int J, int L>
+PSLA_HD void dit_butterfly(float& ar, float& ai, float& br, float& bi) {
+    constexpr int j = ((J % L) + L) % L;
+    if constexpr (j == 0) {
+        const float xr = ar - br, xi = ai - bi;
+        ar += br;
+        ai += bi;
+        br = xr;
+        bi = xi;
+    } else if constexpr (4 * j == L) {  // W = -i:  W*b = (b_i, -b_r)
+        const float xr = ar - bi, xi = ai + br;
+        ar += bi;
+        ai -= br;
+        br = xr;
+        bi = xi;
     } else {
-        constexpr float wr = Twiddle<k, N>::re, wi = Twiddle<k, N>::im;
-        float t = ar * wr - ai * wi;
-        ai = ar * wi + ai * wr;
-        ar = t;
+        constexpr double c = ct_cos2pi(j, L), sn = -ct_sin2pi(j, L);
+        constexpr bool big_c = (c < 0 ? -c : c) >= (sn < 0 ? -sn : sn);
+        float pr, pi, m;
+        if constexpr (8 * j == L) {  // c = -s = sqrt(1/2)
+            pr = br + bi;
+            pi = bi - br;
+            m = static_cast<float>(c);
+        } else if constexpr (8 * j == 3 * L) {  // c = s = -sqrt(1/2)
+            pr = br - bi;
+            pi = bi + br;
+            m = static_cast<float>(c);
+        } else if constexpr (big_c) {
+            constexpr float t = static_cast<float>(sn / c);
+            pr = fmaf(-t, bi, br);
+            pi = fmaf(t, br, bi);
+            m = static_cast<float>(c);
+        } else {
+            constexpr float t = static_cast<float>(c / sn);
+            pr = fmaf(t, br, -bi);
+            pi = fmaf(t, bi, br);
+            m = static_cast<float>(sn);
+        }
+        br = fmaf(-m, pr, ar);
+        bi = fmaf(-m, pi, ai);
+        ar = fmaf(m, pr, ar);
+        ai = fmaf(m, pi, ai);
     }
 }
 
-// In-place decimation-in-frequency FFT of length N (power of two) on register arrays.
-// Input natural order; output bit-reversed: X[brev<log2 N>(r)] = (re[r], im[r]).
-template <int N, int LEN = N>
-PSLA_HD void fft_dif(float (&re)[N], float (&im)[N]) {
-    if constexpr (LEN >= 2) {
+template <int N, int BITS, int NZ = N, int LEN = 2>
+PSLA_HD void fft_dit(float (&re)[N], float (&im)[N]) {
+    if constexpr (LEN <= N) {
         constexpr int HALF = LEN / 2;
         static_for<0, N / LEN>([&](auto blk_) {
             constexpr int base = decltype(blk_)::value * LEN;
             static_for<0, HALF>([&](auto j_) {
                 constexpr int j = decltype(j_)::value;
-                constexpr int p = base + j, q = base + j + HALF;
-                float ur = re[p], ui = im[p], vr = re[q], vi = im[q];
-                re[p] = ur + vr;
-                im[p] = ui + vi;
-                float dr = ur - vr, di = ui - vi;
-                mul_twiddle<j, LEN>(dr, di);
-                re[q] = dr;
-                im[q] = di;
+                constexpr int p = brev<BITS>(base + j), q = brev<BITS>(base + j + HALF);  // registers holding y[base+j], y[..+HALF]
+                if constexpr (LEN == 2 && q >= NZ) {  // x[q] == 0: both outputs equal x[p]
+                    re[q] = re[p];
+                    im[q] = im[p];
+                } else {
+                    dit_butterfly<j, LEN>(re[p], im[p], re[q], im[q]);
+                }
             });
         });
-        fft_dif<N, HALF>(re, im);
+        fft_dit<N, BITS, NZ, 2 * LEN>(re, im);
     }
 }
 

@@ -448,11 +448,17 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
     p.nmel = h->nmel;
     p.norm_mean = norm_mean;
     p.norm_div = norm_div;
-    p.norm_rdiv = 1.0f / norm_div;
-    // the value every masked / padded cell takes: (0 - mean) / std evaluated like torch does (fp32 sub, IEEE div)
+    // the value every masked / padded cell takes: (0 - mean) / std evaluated like torch does (fp32 sub, IEEE div);
+    // likewise the value of a cell on the log floor, log(max(e, eps)) with e <= eps
     {
+        const float log_eps = -15.9423847198486328f;  // fp32 log(1.1920929e-07)
         volatile float z = 0.0f - norm_mean;
+        volatile float f = log_eps - norm_mean;
         p.fill = skip_norm ? 0.0f : z / norm_div;
+        p.floor_val = skip_norm ? log_eps : f / norm_div;
+        const double ln2 = 0.693147180559945309417;
+        p.log_scale = skip_norm ? static_cast<float>(ln2) : static_cast<float>(ln2 / static_cast<double>(norm_div));
+        p.log_bias = skip_norm ? 0.0f : static_cast<float>(-static_cast<double>(norm_mean) / static_cast<double>(norm_div));
     }
     p.skip_norm = skip_norm ? 1 : 0;
     p.fast_log = h->fast_log;

@@ -53,7 +53,9 @@ struct StreamParams {
     int T;  // target_length
     int G;  // groups per clip = ceil(T / 4)
     int nmel;
-    float norm_mean, norm_div, norm_rdiv, fill;  // fill = (0 - mean) / div in IEEE fp32 (0 if skip_norm)
+    float norm_mean, norm_div, fill;  // fill = (0 - mean) / div in IEEE fp32 (0 if skip_norm)
+    float floor_val;                  // (log(eps) - mean) / div in IEEE fp32: the value of a cell on the log floor
+    float log_scale, log_bias;        // fast log: value = lg2(e) * log_scale + log_bias
     int skip_norm;
     int fast_log;
     float preemph, c1;
@@ -168,8 +170,11 @@ __global__ void __launch_bounds__(256) clip_stats_kernel(const float* __restrict
 // ------------------------------------------------------------------------------------------------
 enum ClipStateWord {
     CS_N1 = 0, CS_NMIN, CS_L1, CS_L2, CS_SUB1, CS_MEAN2, CS_MIXMEAN, CS_FLAGS, CS_F0, CS_F1, CS_T0, CS_T1, CS_MEFF,
-    CS_ALO, CS_AHI, CS_BLO, CS_OFF1 /* 2 words */, CS_OFF1_HI, CS_OFF2 /* 2 words */, CS_OFF2_HI, CS_END
+    CS_ALO, CS_AHI, CS_BLO, CS_OFF1 /* 2 words */, CS_OFF1_HI, CS_OFF2 /* 2 words */, CS_OFF2_HI,
+    // loop state of the warp (same reason: nothing may stay live in registers across the FFT phases)
+    CS_B, CS_G, CS_BUDGET, CS_NEXT /* kNext* bits for the group being processed */, CS_CARRY, CS_END
 };
+constexpr int kNextLive = 1, kNextFull = 2;
 static_assert(CS_END <= kCsWords && CS_OFF1 % 2 == 0 && CS_OFF2 % 2 == 0, "clip-state layout");
 constexpr int kCsMix = 8;  // CS_FLAGS: kFlagAligned1 | kFlagAligned2 | kCsMix
 
@@ -440,15 +445,17 @@ __device__ __forceinline__ void enter_clip(const StreamParams& p, int b, int lan
     __syncwarp();
 }
 
-// log floor, SpecAugment fill, normalisation, coalesced streaming stores of the group's 4 rows
-template <bool FASTLOG>
+// log floor, SpecAugment fill, normalisation, coalesced streaming stores of the group's 4 rows.
+//   FASTLOG   (ln(e) - mean) / div  =  lg2(e) * (ln2 / div) - mean / div : one MUFU.LG2 and one FMA per cell (abs error
+//             ~1e-6 in log-mel units); cells on the float-epsilon floor take the host-computed IEEE constant, so they
+//             stay bit-identical to the reference.
+//   !FASTLOG  logf + IEEE subtraction / division, the reference's expression verbatim.
+template <bool FASTLOG, bool ALLBINS>
 __device__ __forceinline__ void epilogue(const StreamParams& p, const int* cs, const int* mel_bin, int lane, int f0, float* __restrict__ out,
                                          const float (&acc)[kMelSlots][kGroupFrames]) {
-    const float eps = 1.1920928955078125e-07f;    // kaldi.py:22
-    const float log_eps = -15.9423847198486328f;  // fp32 log(eps): what max(x, eps).log() gives on the floor
-    const float mean = p.skip_norm ? 0.f : p.norm_mean;
-    const float div = p.skip_norm ? 1.f : p.norm_div;
-    const float rdiv = p.skip_norm ? 1.f : p.norm_rdiv;
+    const float eps = 1.1920928955078125e-07f;  // kaldi.py:22
+    const float fill = p.fill, floor_val = p.floor_val, la = p.log_scale, lb = p.log_bias;
+    const int nmel = p.nmel;
     const int mf0 = cs_i(cs, CS_F0), mf1 = cs_i(cs, CS_F1), t0 = cs_i(cs, CS_T0), t1 = cs_i(cs, CS_T1), m_eff = cs_i(cs, CS_MEFF);
     int mbin[kMelSlots];
     bool keep[kMelSlots];  // column survives the frequency mask
@@ -457,44 +464,46 @@ __device__ __forceinline__ void epilogue(const StreamParams& p, const int* cs, c
         mbin[i] = mel_bin[32 * i + lane];
         keep[i] = !(mbin[i] >= mf0 && mbin[i] < mf1);
     }
+    float* orow = out + static_cast<size_t>(f0) * nmel;
+    const int rows = min(kGroupFrames, p.T - f0);
 #pragma unroll
     for (int q = 0; q < kGroupFrames; ++q) {
-        const int row = f0 + q;
-        const bool rlive = row < m_eff && !(row >= t0 && row < t1);
-        if (row < p.T) {
-            float* orow = out + static_cast<size_t>(row) * p.nmel;
+        if (q < rows) {  // warp-uniform
+            const int row = f0 + q;
+            const bool rlive = row < m_eff && !(row >= t0 && row < t1);
 #pragma unroll
             for (int i = 0; i < kMelSlots; ++i) {
                 const float e = acc[i][q];
                 float v;
-                if (FASTLOG) {
-                    const float lg = (e > eps) ? __logf(e) : log_eps;
-                    // (lg - mean) / div as a Newton-corrected multiply by 1/div: correctly rounded but for rare
-                    // last-bit cases; live cells only need 1e-3, the fill constant is the exact IEEE quotient
-                    const float x = __fsub_rn(lg, mean);
-                    const float q0 = x * rdiv;
-                    v = fmaf(fmaf(-q0, div, x), rdiv, q0);
+                if (FASTLOG) {  // branch-free: the log of a floored / dead cell is computed and discarded
+                    v = fmaf(__log2f(fmaxf(e, eps)), la, lb);
+                    v = (e > eps) ? v : floor_val;
                 } else {
                     const float lg = logf(fmaxf(e, eps));
                     v = p.skip_norm ? lg : __fdiv_rn(__fsub_rn(lg, p.norm_mean), p.norm_div);
                 }
-                if (mbin[i] >= 0) __stcs(orow + mbin[i], (rlive && keep[i]) ? v : p.fill);
+                v = (rlive && keep[i]) ? v : fill;
+                if (ALLBINS || mbin[i] >= 0) __stcs(orow + mbin[i], v);
             }
         }
+        orow += nmel;
     }
 }
 
-// one live group: frame means, pass 1, (shift), pass 2, power, (prefetch), mel, epilogue, (commit)
-template <bool EXACT, bool MELSPEC, bool FULLNEXT>
-__device__ __forceinline__ void process_group(const StreamParams& p, const float* TAB, float* WS, int lane, int f0, bool next_live,
-                                              float* __restrict__ out, float& carry) {
+__device__ __forceinline__ void cs_set(int* cs, int w, int v, int lane) {
+    if (lane == 0) *reinterpret_cast<volatile int*>(cs + w) = v;
+}
+
+// one live group: frame means, pass 1, (shift), pass 2, power, (prefetch), mel, epilogue, (commit).
+// Everything it needs beyond the kernel parameters comes from the warp's shared-memory state (CS_*).
+template <bool EXACT, bool MELSPEC>
+__device__ __forceinline__ void process_group(const StreamParams& p, const float* TAB, float* WS, int lane) {
     float* D = WS + kWsD;
     float* BS = WS + kWsBS;
     float* XS = WS + kWsXS;
-    const int* cs = reinterpret_cast<const int*>(WS + kWsCS);
+    int* cs = reinterpret_cast<int*>(WS + kWsCS);
     float* EX = WS + kWsEX;
     const int h = lane >> 4, n2 = lane & 15;
-    const int S0 = f0 * kFrameShift;
 
     // per-frame means (kaldi.py:183-186) from the 16-sample block sums: lane 8 f + j adds 3 (4) blocks, xor tree
     float cmu_x, cmu_y;
@@ -511,7 +520,7 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
     }
     pair_pass1(n2, h, D, XS, TAB + kTabWin, TAB + kTabTwz, EX + h * kExSecondPair, cmu_x, cmu_y);
     __syncwarp();
-    if (next_live) stage_shift(lane, D, BS, XS);
+    if (cs_i(cs, CS_NEXT) & kNextLive) stage_shift(lane, D, BS, XS);
     {
         // pass 2 re-maps the lanes: pair h2 = lane & 1, row t = lane >> 1 (see kExSecondPair)
         const int h2 = lane & 1, t = lane >> 1;
@@ -523,9 +532,12 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
     __syncwarp();
     constexpr int NIT = StageGeom<kOverlapSamples>::kIters;
     float4 ra[NIT], rc[NIT];
-    if (next_live) {
+    const int next = cs_i(cs, CS_NEXT);
+    if (next & kNextLive) {  // prefetch the next group's 640 new samples; they are consumed after the epilogue
         const MixState m = load_mix(cs, p.wav);
-        stage_issue<kOverlapSamples, FULLNEXT>(m, S0 + kStepSamples, lane, ra, rc);
+        const int S1 = (cs_i(cs, CS_G) + 1) * kStepSamples;
+        if (next & kNextFull) stage_issue<kOverlapSamples, true>(m, S1, lane, ra, rc);
+        else stage_issue<kOverlapSamples, false>(m, S1, lane, ra, rc);
     }
     float acc[kMelSlots][kGroupFrames];
     {
@@ -536,12 +548,21 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
         mt.w = TAB + kTabMelW;
         warp_mel<MELSPEC>(lane, EX, mt, acc);
     }
-    const int* mel_bin = reinterpret_cast<const int*>(TAB + kTabMelBin);
-    if (p.fast_log) epilogue<true>(p, cs, mel_bin, lane, f0, out, acc);
-    else epilogue<false>(p, cs, mel_bin, lane, f0, out, acc);
-    if (next_live) {
+    {
+        const int f0 = cs_i(cs, CS_G) * kGroupFrames;
+        float* out = p.out + static_cast<size_t>(cs_i(cs, CS_B)) * p.T * p.nmel;
+        const int* mel_bin = reinterpret_cast<const int*>(TAB + kTabMelBin);
+        // MELSPEC is only selected for 128 mel bins: every (slot, lane) then owns a column
+        if (p.fast_log) epilogue<true, MELSPEC>(p, cs, mel_bin, lane, f0, out, acc);
+        else epilogue<false, MELSPEC>(p, cs, mel_bin, lane, f0, out, acc);
+    }
+    if (next & kNextLive) {
         const MixState m = load_mix(cs, p.wav);
-        stage_commit<EXACT, kOverlapSamples, FULLNEXT>(m, S0 + kStepSamples, lane, p.preemph, p.c1, ra, rc, D, BS, XS, carry);
+        const int S1 = (cs_i(cs, CS_G) + 1) * kStepSamples;
+        float carry = cs_f(cs, CS_CARRY);
+        if (next & kNextFull) stage_commit<EXACT, kOverlapSamples, true>(m, S1, lane, p.preemph, p.c1, ra, rc, D, BS, XS, carry);
+        else stage_commit<EXACT, kOverlapSamples, false>(m, S1, lane, p.preemph, p.c1, ra, rc, D, BS, XS, carry);
+        cs_set(cs, CS_CARRY, __float_as_int(carry), lane);
     }
     __syncwarp();
 }
@@ -565,57 +586,61 @@ __global__ void __launch_bounds__(kThreads, 1) fbank_stream_kernel(const StreamP
     __syncthreads();
 
     // ---- this warp's share of the work ----
-    int b, g, budget;
     {
         const long long W = static_cast<long long>(gridDim.x) * kWarpsPerCta;
         const long long r = static_cast<long long>(warp) * gridDim.x + blockIdx.x;  // neighbouring ranges on different SMs
         const long long c_lo = p.total_cost * r / W, c_hi = p.total_cost * (r + 1) / W;
         if (c_lo >= c_hi) return;
+        int b, g;
         const long long start_cost = find_start(p.cost, p.n_clips, p.G, c_lo, b, g);
-        budget = static_cast<int>(c_hi - start_cost);  // groups are taken while the cost consumed so far is < budget
+        cs_set(cs, CS_B, b, lane);
+        cs_set(cs, CS_G, g, lane);
+        cs_set(cs, CS_BUDGET, static_cast<int>(c_hi - start_cost), lane);  // groups are taken while the cost consumed is < budget
+        __syncwarp();
     }
     int loaded_b = -1;
-    bool staged = false;  // the window holds the samples of group g
-    float carry = 0.f;
+    bool staged = false;  // the window holds the samples of the current group
 
-    while (b < p.n_clips && budget > 0) {
+    while (true) {
+        const int b = cs_i(cs, CS_B), g = cs_i(cs, CS_G);
+        int budget = cs_i(cs, CS_BUDGET);
+        if (b >= p.n_clips || budget <= 0) break;
         if (b != loaded_b) {
             enter_clip<EXACT>(p, b, lane, cs);
             loaded_b = b;
             staged = false;
         }
         const int f0 = kGroupFrames * g;
-        float* out = p.out + static_cast<size_t>(b) * p.T * p.nmel;
-        if (group_dead(cs, g)) {
-            store_fill_rows(out, f0, p.T, p.nmel, lane, p.fill);
+        const bool dead = group_dead(cs, g);
+        bool next_live = false;
+        if (dead) {
+            store_fill_rows(p.out + static_cast<size_t>(b) * p.T * p.nmel, f0, p.T, p.nmel, lane, p.fill);
             budget -= 1;
-            staged = false;
         } else {
-            const int S0 = f0 * kFrameShift;
+            const MixState m = load_mix(cs, p.wav);
             if (!staged) {  // cold start of a run of groups
-                const MixState m = load_mix(cs, p.wav);
                 constexpr int NIT0 = StageGeom<0>::kIters;
                 float4 ra[NIT0], rc[NIT0];
-                carry = 0.f;
-                stage_issue<0, false>(m, S0, lane, ra, rc);
-                stage_commit<EXACT, 0, false>(m, S0, lane, p.preemph, p.c1, ra, rc, WS + kWsD, WS + kWsBS, WS + kWsXS, carry);
-                __syncwarp();
+                float carry = 0.f;
+                stage_issue<0, false>(m, f0 * kFrameShift, lane, ra, rc);
+                stage_commit<EXACT, 0, false>(m, f0 * kFrameShift, lane, p.preemph, p.c1, ra, rc, WS + kWsD, WS + kWsBS, WS + kWsXS, carry);
+                cs_set(cs, CS_CARRY, __float_as_int(carry), lane);
             }
             budget -= kLiveCost;
-            const bool next_live = (g + 1 < p.G) && !group_dead(cs, g + 1) && budget > 0;
-            bool full_next = false;
-            if (next_live) {
-                const MixState m = load_mix(cs, p.wav);
-                full_next = window_full(m, S0 + kStepSamples);
-            }
-            if (full_next) process_group<EXACT, MELSPEC, true>(p, TAB, WS, lane, f0, next_live, out, carry);
-            else process_group<EXACT, MELSPEC, false>(p, TAB, WS, lane, f0, next_live, out, carry);
-            staged = next_live;
+            next_live = (g + 1 < p.G) && !group_dead(cs, g + 1) && budget > 0;
+            const bool full_next = next_live && window_full(m, (g + 1) * kStepSamples);
+            cs_set(cs, CS_NEXT, (next_live ? kNextLive : 0) | (full_next ? kNextFull : 0), lane);
         }
-        if (++g == p.G) {
-            g = 0;
-            ++b;
-        }
+        cs_set(cs, CS_BUDGET, budget, lane);
+        __syncwarp();
+        if (!dead) process_group<EXACT, MELSPEC>(p, TAB, WS, lane);
+        staged = next_live;
+        // advance (CS_B / CS_G are read by process_group, so they move only now)
+        const int g1 = cs_i(cs, CS_G) + 1;
+        const bool wrap = g1 == p.G;
+        cs_set(cs, CS_G, wrap ? 0 : g1, lane);
+        if (wrap) cs_set(cs, CS_B, cs_i(cs, CS_B) + 1, lane);
+        __syncwarp();
     }
 }
 

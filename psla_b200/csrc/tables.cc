@@ -76,7 +76,7 @@ bool build_table_buffer(const float* window, const float* mel_dense, int num_bin
         slot_max[i] = mx;
     }
     const int spec[kMelSlots] = {kMelSpec0, kMelSpec1, kMelSpec2, kMelSpec3};
-    bool fits = true;
+    bool fits = num_bins == kMaxMel;  // the unrolled path also assumes that every (slot, lane) owns a mel bin
     for (int i = 0; i < kMelSlots; ++i) fits = fits && slot_max[i] <= spec[i];
     if (fits)  // the unrolled path always runs its compile-time tap counts (weights are zero padded)
         for (int i = 0; i < kMelSlots; ++i) slot_max[i] = spec[i];

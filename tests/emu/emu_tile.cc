@@ -137,16 +137,16 @@ void emu_fft(int n, const float* in_re, const float* in_im, float* out_re, float
     if (n == 32 || n == -32) {
         float re[32], im[32];
         for (int i = 0; i < 32; ++i) { re[i] = in_re[i]; im[i] = in_im[i]; }
-        if (n == 32) fft_dif<32>(re, im);
+        if (n == 32) fft_dit<32, 5>(re, im);
         else {
             for (int i = 25; i < 32; ++i) re[i] = im[i] = 0.f;
-            fft32_zero_tail(re, im);
+            fft_dit<32, 5, 25>(re, im);
         }
         for (int r = 0; r < 32; ++r) { out_re[brev<5>(r)] = re[r]; out_im[brev<5>(r)] = im[r]; }
     } else {
         float re[16], im[16];
         for (int i = 0; i < 16; ++i) { re[i] = in_re[i]; im[i] = in_im[i]; }
-        fft_dif<16>(re, im);
+        fft_dit<16, 4>(re, im);
         for (int r = 0; r < 16; ++r) { out_re[brev<4>(r)] = re[r]; out_im[brev<4>(r)] = im[r]; }
     }
 }

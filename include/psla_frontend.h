@@ -107,6 +107,15 @@ int psla_frontend_set_exact_clip_mean(psla_frontend_t* handle, int enable);
 int psla_frontend_set_timing(psla_frontend_t* handle, int enable);
 int psla_frontend_get_timing(psla_frontend_t* handle, double* stats_ms, double* tile_ms, int64_t* n_forward);
 
+/* Optional per-warp timeline of the streaming kernel (tracing aid; the reference has no counterpart).  While a DEVICE
+ * buffer of psla_frontend_trace_records() records x 4 int64 is installed, every warp of every forward() writes
+ *   [0] globaltimer ns at warp start   [1] globaltimer ns at warp end
+ *   [2] cycles before its first group | total cycles << 32
+ *   [3] smid | groups computed << 16 | constant (masked / padded) groups << 32 | cold starts << 48
+ * Pass NULL to switch it off. */
+int psla_frontend_set_trace(psla_frontend_t* handle, int64_t* device_buf, size_t capacity_records);
+int psla_frontend_trace_records(const psla_frontend_t* handle);
+
 const char* psla_strerror(int status);
 int psla_last_cuda_error(const psla_frontend_t* handle);
 const char* psla_version(void);

@@ -35,6 +35,8 @@ SYMBOLS = {
     "psla_frontend_set_exact_clip_mean": (c_int, [c_void_p, c_int]),
     "psla_frontend_set_timing": (c_int, [c_void_p, c_int]),
     "psla_frontend_get_timing": (c_int, [c_void_p, POINTER(c_double), POINTER(c_double), POINTER(c_int64)]),
+    "psla_frontend_set_trace": (c_int, [c_void_p, c_void_p, c_size_t]),
+    "psla_frontend_trace_records": (c_int, [c_void_p]),
     "psla_strerror": (c_char_p, [c_int]),
     "psla_last_cuda_error": (c_int, [c_void_p]),
     "psla_version": (c_char_p, []),

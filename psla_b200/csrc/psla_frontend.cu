@@ -48,6 +48,7 @@ struct psla_frontend {
     bool mel_spec = false;
     int num_sms = 0;
     int timing = 0;
+    long long* trace = nullptr;  // device buffer of the optional per-warp timeline
     struct EvTriple {
         cudaEvent_t e[3];
     };
@@ -279,6 +280,19 @@ int psla_frontend_get_timing(psla_frontend_t* h, double* stats_ms, double* tile_
     return PSLA_OK;
 }
 
+int psla_frontend_set_trace(psla_frontend_t* h, int64_t* device_buf, size_t capacity_records) {
+    if (!h) return PSLA_E_INVALID;
+    const size_t need = static_cast<size_t>(h->num_sms > 0 ? h->num_sms : 148) * kWarpsPerCta;
+    if (device_buf && capacity_records < need) return PSLA_E_WORKSPACE;
+    static_assert(sizeof(long long) == sizeof(int64_t), "trace word");
+    h->trace = reinterpret_cast<long long*>(device_buf);
+    return PSLA_OK;
+}
+
+int psla_frontend_trace_records(const psla_frontend_t* h) {
+    return h ? (h->num_sms > 0 ? h->num_sms : 148) * kWarpsPerCta : 0;
+}
+
 int psla_frontend_set_fast_log(psla_frontend_t* h, int enable) {
     if (!h) return PSLA_E_INVALID;
     h->fast_log = enable ? 1 : 0;
@@ -464,6 +478,7 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
     p.fast_log = h->fast_log;
     p.preemph = h->preemph;
     p.c1 = static_cast<float>(1.0 - static_cast<double>(h->preemph));
+    p.trace = h->trace;
     const dim3 grid(h->num_sms > 0 ? h->num_sms : 148);
     if (h->exact_mean) {
         if (h->mel_spec) fbank_stream_kernel<true, true><<<grid, kThreads, h->smem_bytes, stream>>>(p);

@@ -59,7 +59,10 @@ struct StreamParams {
     int skip_norm;
     int fast_log;
     float preemph, c1;
+    long long* trace;  // optional [gridDim.x * kWarpsPerCta][kTraceWords] per-warp timeline (psla_frontend_set_trace), else nullptr
 };
+constexpr int kTraceWords = 4;  // globaltimer at warp start / end (ns), clock64 cycles before the first group | total << 32,
+                                // smid | live groups << 16 | dead groups << 32 | cold starts << 48
 
 __device__ __forceinline__ ClipDesc load_desc(const ClipDesc* __restrict__ p) {
     union {
@@ -172,10 +175,11 @@ enum ClipStateWord {
     CS_N1 = 0, CS_NMIN, CS_L1, CS_L2, CS_SUB1, CS_MEAN2, CS_MIXMEAN, CS_FLAGS, CS_F0, CS_F1, CS_T0, CS_T1, CS_MEFF,
     CS_ALO, CS_AHI, CS_BLO, CS_OFF1 /* 2 words */, CS_OFF1_HI, CS_OFF2 /* 2 words */, CS_OFF2_HI,
     // loop state of the warp (same reason: nothing may stay live in registers across the FFT phases)
-    CS_B, CS_G, CS_BUDGET, CS_NEXT /* kNext* bits for the group being processed */, CS_CARRY, CS_END
+    CS_B, CS_G, CS_BUDGET, CS_NEXT /* kNext* bits for the group being processed */, CS_CARRY,
+    CS_TR_LIVE, CS_TR_DEAD, CS_TR_COLD, CS_TR_T0 /* 2 words */, CS_TR_T0_HI, CS_TR_C0 /* 2 words */, CS_TR_C0_HI, CS_END
 };
 constexpr int kNextLive = 1, kNextFull = 2;
-static_assert(CS_END <= kCsWords && CS_OFF1 % 2 == 0 && CS_OFF2 % 2 == 0, "clip-state layout");
+static_assert(CS_END <= kCsWords && CS_OFF1 % 2 == 0 && CS_OFF2 % 2 == 0 && CS_TR_T0 % 2 == 0 && CS_TR_C0 % 2 == 0, "clip-state layout");
 constexpr int kCsMix = 8;  // CS_FLAGS: kFlagAligned1 | kFlagAligned2 | kCsMix
 
 __device__ __forceinline__ int cs_i(const int* cs, int w) { return *reinterpret_cast<const volatile int*>(cs + w); }
@@ -494,6 +498,52 @@ __device__ __forceinline__ void cs_set(int* cs, int w, int v, int lane) {
     if (lane == 0) *reinterpret_cast<volatile int*>(cs + w) = v;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Optional per-warp timeline (StreamParams::trace): where the time of a launch goes, warp by warp.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ long long global_ns() {
+    long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ void trace_begin(int* cs, int lane) {
+    if (lane == 0) {
+        *reinterpret_cast<volatile long long*>(cs + CS_TR_T0) = global_ns();
+        *reinterpret_cast<volatile long long*>(cs + CS_TR_C0) = clock64();
+        cs[CS_TR_LIVE] = 0;
+        cs[CS_TR_DEAD] = 0;
+        cs[CS_TR_COLD] = 0;
+    }
+    __syncwarp();
+}
+__device__ __forceinline__ void trace_mark(int* cs, int lane) {  // end of the prologue: C0 := cycles spent so far
+    if (lane == 0) {
+        const long long c0 = cs_ll(cs, CS_TR_C0);
+        // low word: prologue cycles; the start clock stays recoverable as (now - prologue)
+        *reinterpret_cast<volatile long long*>(cs + CS_TR_C0) = (c0 & ((1ll << 40) - 1)) | ((clock64() - c0) << 40);
+    }
+    __syncwarp();
+}
+__device__ __forceinline__ void trace_count(int* cs, int lane, int word) {
+    if (lane == 0) *reinterpret_cast<volatile int*>(cs + word) = cs_i(cs, word) + 1;
+}
+__device__ __forceinline__ void trace_end(const StreamParams& p, const int* cs, int lane, int warp) {
+    __syncwarp();
+    if (lane == 0) {
+        const long long packed = cs_ll(cs, CS_TR_C0);
+        const long long c0 = packed & ((1ll << 40) - 1), pro = static_cast<unsigned long long>(packed) >> 40;
+        const long long total = (clock64() - c0) & ((1ll << 40) - 1);
+        unsigned smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        long long* t = p.trace + (static_cast<size_t>(blockIdx.x) * kWarpsPerCta + warp) * kTraceWords;
+        t[0] = cs_ll(cs, CS_TR_T0);
+        t[1] = global_ns();
+        t[2] = pro | (total << 32);
+        t[3] = static_cast<long long>(smid) | (static_cast<long long>(cs_i(cs, CS_TR_LIVE) + cs_i(cs, CS_TR_COLD)) << 16) |
+               (static_cast<long long>(cs_i(cs, CS_TR_DEAD)) << 32) | (static_cast<long long>(cs_i(cs, CS_TR_COLD)) << 48);
+    }
+}
+
 // one live group: frame means, pass 1, (shift), pass 2, power, (prefetch), mel, epilogue, (commit).
 // Everything it needs beyond the kernel parameters comes from the warp's shared-memory state (CS_*).
 template <bool EXACT, bool MELSPEC>
@@ -585,12 +635,16 @@ __global__ void __launch_bounds__(kThreads, 1) fbank_stream_kernel(const StreamP
     }
     __syncthreads();
 
+    if (p.trace) trace_begin(cs, lane);
     // ---- this warp's share of the work ----
     {
         const long long W = static_cast<long long>(gridDim.x) * kWarpsPerCta;
         const long long r = static_cast<long long>(warp) * gridDim.x + blockIdx.x;  // neighbouring ranges on different SMs
         const long long c_lo = p.total_cost * r / W, c_hi = p.total_cost * (r + 1) / W;
-        if (c_lo >= c_hi) return;
+        if (c_lo >= c_hi) {
+            if (p.trace) trace_end(p, cs, lane, warp);
+            return;
+        }
         int b, g;
         const long long start_cost = find_start(p.cost, p.n_clips, p.G, c_lo, b, g);
         cs_set(cs, CS_B, b, lane);
@@ -600,6 +654,7 @@ __global__ void __launch_bounds__(kThreads, 1) fbank_stream_kernel(const StreamP
     }
     int loaded_b = -1;
     bool staged = false;  // the window holds the samples of the current group
+    if (p.trace) trace_mark(cs, lane);
 
     while (true) {
         const int b = cs_i(cs, CS_B), g = cs_i(cs, CS_G);
@@ -613,6 +668,7 @@ __global__ void __launch_bounds__(kThreads, 1) fbank_stream_kernel(const StreamP
         const int f0 = kGroupFrames * g;
         const bool dead = group_dead(cs, g);
         bool next_live = false;
+        if (p.trace) trace_count(cs, lane, dead ? CS_TR_DEAD : (staged ? CS_TR_LIVE : CS_TR_COLD));
         if (dead) {
             store_fill_rows(p.out + static_cast<size_t>(b) * p.T * p.nmel, f0, p.T, p.nmel, lane, p.fill);
             budget -= 1;
@@ -642,6 +698,7 @@ __global__ void __launch_bounds__(kThreads, 1) fbank_stream_kernel(const StreamP
         if (wrap) cs_set(cs, CS_B, cs_i(cs, CS_B) + 1, lane);
         __syncwarp();
     }
+    if (p.trace) trace_end(p, cs, lane, warp);
 }
 
 }  // namespace psla

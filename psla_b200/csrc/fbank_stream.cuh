@@ -97,9 +97,9 @@ constexpr int kWsD = 0;
 constexpr int kWsBS = kWsD + kDFloats;
 constexpr int kWsXS = kWsBS + kBsFloats;
 constexpr int kWsCS = kWsXS + kXsFloats;  // per-clip state of the warp (kept out of the register file, see stream_kernel.cuh)
-constexpr int kCsWords = 32;
+constexpr int kCsWords = 36;
 constexpr int kWsEX = kWsCS + kCsWords;
-constexpr int kWarpFloats = kWsEX + kExFloats;  // 3328 floats = 13312 B
+constexpr int kWarpFloats = kWsEX + kExFloats;  // 3332 floats = 13328 B
 static_assert((kWsEX * 4) % 16 == 0 && (kWarpFloats * 4) % 16 == 0, "16-byte alignment of vector regions");
 
 // Constant tables (floats), copied once per CTA into shared memory.

@@ -49,6 +49,7 @@ struct psla_frontend {
     int num_sms = 0;
     int timing = 0;
     long long* trace = nullptr;  // device buffer of the optional per-warp timeline
+    CostModel cm = kDefaultCost;  // work-partition weights (psla_frontend_set_cost_model)
     struct EvTriple {
         cudaEvent_t e[3];
     };
@@ -282,7 +283,7 @@ int psla_frontend_get_timing(psla_frontend_t* h, double* stats_ms, double* tile_
 
 int psla_frontend_set_trace(psla_frontend_t* h, int64_t* device_buf, size_t capacity_records) {
     if (!h) return PSLA_E_INVALID;
-    const size_t need = static_cast<size_t>(h->num_sms > 0 ? h->num_sms : 148) * kWarpsPerCta;
+    const size_t need = static_cast<size_t>(h->num_sms > 0 ? h->num_sms : 148) * kWarpsPerCta * (kTraceWords / 4);
     if (device_buf && capacity_records < need) return PSLA_E_WORKSPACE;
     static_assert(sizeof(long long) == sizeof(int64_t), "trace word");
     h->trace = reinterpret_cast<long long*>(device_buf);
@@ -290,7 +291,16 @@ int psla_frontend_set_trace(psla_frontend_t* h, int64_t* device_buf, size_t capa
 }
 
 int psla_frontend_trace_records(const psla_frontend_t* h) {
-    return h ? (h->num_sms > 0 ? h->num_sms : 148) * kWarpsPerCta : 0;
+    return h ? (h->num_sms > 0 ? h->num_sms : 148) * kWarpsPerCta * (kTraceWords / 4) : 0;
+}
+
+int psla_frontend_set_cost_model(psla_frontend_t* h, int live, int dead, int cold) {
+    // total cost of a batch must stay well inside int64 and a warp's budget inside int32
+    if (!h || live < 1 || dead < 1 || cold < 0 || live > 4096 || dead > 4096 || cold > 4096) return PSLA_E_INVALID;
+    h->cm.live = live;
+    h->cm.dead = dead;
+    h->cm.cold = cold;
+    return PSLA_OK;
 }
 
 int psla_frontend_set_fast_log(psla_frontend_t* h, int enable) {
@@ -420,7 +430,7 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
         cst.b_lo = b_lo;
         cst.pad = 0;
         cst.pad2 = 0;
-        total_cost += static_cast<long long>(kLiveCost) * G - static_cast<long long>(kLiveCost - 1) * ((a_hi - a_lo) + (G - b_lo));
+        total_cost += cost_before(h->cm, a_lo, a_hi, b_lo, G);
     }
     costs[n_clips].cum = total_cost;
     costs[n_clips].a_lo = costs[n_clips].a_hi = costs[n_clips].b_lo = costs[n_clips].pad = 0;
@@ -478,6 +488,7 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
     p.fast_log = h->fast_log;
     p.preemph = h->preemph;
     p.c1 = static_cast<float>(1.0 - static_cast<double>(h->preemph));
+    p.cm = h->cm;
     p.trace = h->trace;
     const dim3 grid(h->num_sms > 0 ? h->num_sms : 148);
     if (h->exact_mean) {

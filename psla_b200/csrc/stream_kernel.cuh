@@ -24,15 +24,20 @@ struct alignas(16) ClipDesc {  // 64 bytes, one per output clip
 static_assert(sizeof(ClipDesc) == 64, "ClipDesc layout");
 constexpr int kFlagAligned1 = 1, kFlagAligned2 = 2, kFlagStats = 4;
 
-// Work partition: a group (4 output rows) costs kLiveCost if any of its rows carries computed features, 1 if all four
-// are padding / time-masked (constant rows).  Dead groups of a clip are [a_lo, a_hi) and [b_lo, G).
+// Work partition: a group (4 output rows) costs `live` if any of its rows carries computed features (+ `cold` if it is
+// the first group of a run of live groups: its whole 880-sample window is staged without a prefetch), `dead` if all four
+// rows are padding / time-masked (constant rows).  Dead groups of a clip are [a_lo, a_hi) and [b_lo, G).
+struct CostModel {
+    int live, dead, cold;
+};
 struct alignas(16) ClipCost {  // 32 bytes; entry n_clips holds the total in `cum`
     long long cum;  // cost of all clips before this one
     int a_lo, a_hi, b_lo, pad;
     long long pad2;
 };
 static_assert(sizeof(ClipCost) == 32, "ClipCost layout");
-constexpr int kLiveCost = 32;
+// measured on B200 (scripts/gpu_trace.py): a live group ~10.3k cycles, a cold start ~+8k, a dead group ~0.3k in a run
+constexpr CostModel kDefaultCost = {64, 2, 48};
 
 constexpr int kStatSegs = 8;  // partial sums per clip
 constexpr int kStatVals = 3;  // sum(w1), sum(w2), sum(w2[0:min(n1,n2)])
@@ -59,10 +64,14 @@ struct StreamParams {
     int skip_norm;
     int fast_log;
     float preemph, c1;
+    CostModel cm;
     long long* trace;  // optional [gridDim.x * kWarpsPerCta][kTraceWords] per-warp timeline (psla_frontend_set_trace), else nullptr
 };
-constexpr int kTraceWords = 4;  // globaltimer at warp start / end (ns), clock64 cycles before the first group | total << 32,
-                                // smid | live groups << 16 | dead groups << 32 | cold starts << 48
+// words per warp: [0] globaltimer at warp start (ns)  [1] at warp end  [2] clock64 cycles before the first group | total << 32
+// [3] smid | live groups << 16 | dead groups << 32 | cold starts << 48  [4 + i] i-th loop step of the warp (i < kTraceSteps):
+// cycles since warp start | kind << 40 (1 live, 2 cold-started live, 3 run of dead groups) | groups in the step << 44
+constexpr int kTraceSteps = 28;
+constexpr int kTraceWords = 4 + kTraceSteps;
 
 __device__ __forceinline__ ClipDesc load_desc(const ClipDesc* __restrict__ p) {
     union {
@@ -171,20 +180,40 @@ __global__ void __launch_bounds__(256) clip_stats_kernel(const float* __restrict
 // almost the whole 128-register budget, and anything loop-carried would be spilled to local memory around them.
 // Every use is a volatile shared-memory read (so the compiler cannot cache it in a register across the FFT).
 // ------------------------------------------------------------------------------------------------
+// Words that are used together share a 16-byte quad, so one LDS.128 (cs_q) brings them.
 enum ClipStateWord {
-    CS_N1 = 0, CS_NMIN, CS_L1, CS_L2, CS_SUB1, CS_MEAN2, CS_MIXMEAN, CS_FLAGS, CS_F0, CS_F1, CS_T0, CS_T1, CS_MEFF,
-    CS_ALO, CS_AHI, CS_BLO, CS_OFF1 /* 2 words */, CS_OFF1_HI, CS_OFF2 /* 2 words */, CS_OFF2_HI,
+    CS_N1 = 0, CS_NMIN, CS_L1, CS_L2,                                    // quad 0: conditioning
+    CS_SUB1, CS_MEAN2, CS_MIXMEAN, CS_FLAGS,                             // quad 1: conditioning
+    CS_OFF1 /* 2 words */, CS_OFF1_HI, CS_OFF2 /* 2 words */, CS_OFF2_HI,  // quad 2: waveform offsets
+    CS_F0, CS_F1, CS_T0, CS_T1,                                          // quad 3: masks
+    CS_MEFF, CS_ALO, CS_AHI, CS_BLO,                                     // quad 4: live rows / dead group ranges
     // loop state of the warp (same reason: nothing may stay live in registers across the FFT phases)
-    CS_B, CS_G, CS_BUDGET, CS_NEXT /* kNext* bits for the group being processed */, CS_CARRY,
-    CS_TR_LIVE, CS_TR_DEAD, CS_TR_COLD, CS_TR_T0 /* 2 words */, CS_TR_T0_HI, CS_TR_C0 /* 2 words */, CS_TR_C0_HI, CS_END
+    CS_B, CS_G, CS_BUDGET, CS_NEXT /* kNext* bits for the group being processed */,  // quad 5
+    CS_CARRY, CS_TR_LIVE, CS_TR_DEAD, CS_TR_COLD,                        // quad 6
+    CS_TR_T0 /* 2 words */, CS_TR_T0_HI, CS_TR_C0 /* 2 words */, CS_TR_C0_HI, CS_TR_STEP, CS_END
 };
 constexpr int kNextLive = 1, kNextFull = 2;
-static_assert(CS_END <= kCsWords && CS_OFF1 % 2 == 0 && CS_OFF2 % 2 == 0 && CS_TR_T0 % 2 == 0 && CS_TR_C0 % 2 == 0, "clip-state layout");
+static_assert(CS_END <= kCsWords && CS_SUB1 % 4 == 0 && CS_OFF1 % 4 == 0 && CS_F0 % 4 == 0 && CS_MEFF % 4 == 0 && CS_B % 4 == 0 &&
+                  CS_CARRY % 4 == 0 && CS_TR_T0 % 4 == 0 && kWsCS % 4 == 0 && kWarpFloats % 4 == 0,
+              "clip-state layout");
 constexpr int kCsMix = 8;  // CS_FLAGS: kFlagAligned1 | kFlagAligned2 | kCsMix
 
 __device__ __forceinline__ int cs_i(const int* cs, int w) { return *reinterpret_cast<const volatile int*>(cs + w); }
 __device__ __forceinline__ float cs_f(const int* cs, int w) { return __int_as_float(cs_i(cs, w)); }
 __device__ __forceinline__ long long cs_ll(const int* cs, int w) { return *reinterpret_cast<const volatile long long*>(cs + w); }
+// one quad (w % 4 == 0); volatile like the scalar reads
+__device__ __forceinline__ int4 cs_q(const int* cs, int w) {
+    int4 v;
+    asm volatile("ld.volatile.shared.v4.s32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "r"(static_cast<unsigned>(__cvta_generic_to_shared(cs + w))));
+    return v;
+}
+__device__ __forceinline__ void cs_set_q(int* cs, int w, int a, int b, int c, int d) {
+    asm volatile("st.volatile.shared.v4.s32 [%0], {%1, %2, %3, %4};" ::"r"(static_cast<unsigned>(__cvta_generic_to_shared(cs + w))), "r"(a),
+                 "r"(b), "r"(c), "r"(d)
+                 : "memory");
+}
 
 // ------------------------------------------------------------------------------------------------
 // Waveform conditioning of one clip (audioset_dataset.py:91-117).
@@ -211,16 +240,17 @@ struct MixState {
 
 __device__ __forceinline__ MixState load_mix(const int* cs, const float* wav) {
     MixState m;
-    const int fl = cs_i(cs, CS_FLAGS);
-    m.w1 = wav + cs_ll(cs, CS_OFF1);
-    m.w2 = wav + cs_ll(cs, CS_OFF2);
-    m.l1 = cs_f(cs, CS_L1);
-    m.l2 = cs_f(cs, CS_L2);
-    m.sub1 = cs_f(cs, CS_SUB1);
-    m.mean2 = cs_f(cs, CS_MEAN2);
-    m.mixmean = cs_f(cs, CS_MIXMEAN);
-    m.n1 = cs_i(cs, CS_N1);
-    m.nmin = cs_i(cs, CS_NMIN);
+    const int4 q0 = cs_q(cs, CS_N1), q1 = cs_q(cs, CS_SUB1), q2 = cs_q(cs, CS_OFF1);
+    const int fl = q1.w;
+    m.w1 = wav + ((static_cast<long long>(q2.y) << 32) | static_cast<unsigned>(q2.x));
+    m.w2 = wav + ((static_cast<long long>(q2.w) << 32) | static_cast<unsigned>(q2.z));
+    m.n1 = q0.x;
+    m.nmin = q0.y;
+    m.l1 = __int_as_float(q0.z);
+    m.l2 = __int_as_float(q0.w);
+    m.sub1 = __int_as_float(q1.x);
+    m.mean2 = __int_as_float(q1.y);
+    m.mixmean = __int_as_float(q1.z);
     m.mix = (fl & kCsMix) != 0;
     m.al1 = (fl & kFlagAligned1) != 0;
     m.al2 = (fl & kFlagAligned2) != 0;
@@ -334,25 +364,37 @@ __device__ __forceinline__ void stage_shift(int lane, float* __restrict__ D, flo
 }
 
 // ------------------------------------------------------------------------------------------------
-// Work partition helpers (see ClipCost)
+// Work partition helpers (see ClipCost / CostModel).  psla_frontend.cu evaluates the same cost_before() on the host.
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ int cost_before(int a_lo, int a_hi, int b_lo, int g) {  // cost of groups [0, g) of the clip
-    const int d1 = min(max(g, a_lo), a_hi) - a_lo;
-    const int d2 = max(g, b_lo) - b_lo;
-    return kLiveCost * g - (kLiveCost - 1) * (d1 + d2);
-}
-__device__ __forceinline__ bool group_dead(const int* cs, int g) {
-    return (g >= cs_i(cs, CS_ALO) && g < cs_i(cs, CS_AHI)) || g >= cs_i(cs, CS_BLO);
+// the group opens a run of live groups of its clip (group 0, or the group after the dead range [a_lo, a_hi))
+__host__ __device__ __forceinline__ bool run_start(int a_lo, int a_hi, int g) { return g == 0 || (g == a_hi && a_lo < a_hi); }
+__host__ __device__ __forceinline__ bool is_dead(int a_lo, int a_hi, int b_lo, int g) { return (g >= a_lo && g < a_hi) || g >= b_lo; }
+// cost of groups [0, g) of the clip
+__host__ __device__ __forceinline__ int cost_before(const CostModel& cm, int a_lo, int a_hi, int b_lo, int g) {
+    const int ga = g < a_lo ? a_lo : (g > a_hi ? a_hi : g);
+    const int n_dead = (ga - a_lo) + ((g > b_lo ? g : b_lo) - b_lo);
+    const bool has_a = a_lo < a_hi;
+    const int starts = ((g > 0 && (has_a ? a_lo : b_lo) > 0) ? 1 : 0) + ((has_a && a_hi < b_lo && g > a_hi) ? 1 : 0);
+    return cm.live * (g - n_dead) + cm.dead * n_dead + cm.cold * starts;
 }
 
-// first group (b, g) in clip-major order whose preceding cost is >= target; returns that preceding cost
-__device__ __forceinline__ long long find_start(const ClipCost* __restrict__ cost, int n_clips, int G, long long target, int& b_out,
-                                                int& g_out) {
-    int lo = 0, hi = n_clips;  // largest b with cum[b] <= target (cum[0] == 0)
+// First group (b, g) in clip-major order whose preceding cost is >= target; returns that preceding cost.
+// Warp-cooperative (all lanes return the same): the clip is found by a 128-ary search over the cumulative costs, one
+// round trip to L2 per level instead of one per bit.
+__device__ __forceinline__ long long find_start(const ClipCost* __restrict__ cost, const CostModel& cm, int n_clips, int G, long long target,
+                                                int lane, int& b_out, int& g_out) {
+    int lo = 0, hi = n_clips;  // largest b in [lo, hi] with cum[b] <= target (cum[0] == 0)
     while (lo < hi) {
-        const int mid = (lo + hi + 1) >> 1;
-        if (__ldg(&cost[mid].cum) <= target) lo = mid;
-        else hi = mid - 1;
+        const int step = (hi - lo + 127) >> 7;
+        long long v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] = __ldg(&cost[min(hi, lo + (4 * lane + j + 1) * step)].cum);
+        int cnt = 0;  // candidates lo + k*step, k = 1..128 (clipped to hi) are monotone: the first cnt of them pass
+#pragma unroll
+        for (int j = 0; j < 4; ++j) cnt += __popc(__ballot_sync(0xffffffffu, v[j] <= target));
+        const int nlo = min(hi, lo + cnt * step);
+        if (cnt < 128) hi = min(hi, lo + (cnt + 1) * step) - 1;
+        lo = nlo;
     }
     b_out = lo;
     g_out = 0;
@@ -363,7 +405,7 @@ __device__ __forceinline__ long long find_start(const ClipCost* __restrict__ cos
     int glo = 1, ghi = G;  // smallest g with cost_before(g) >= rem  (cost_before(G) > rem)
     while (glo < ghi) {
         const int mid = (glo + ghi) >> 1;
-        if (cost_before(c.a_lo, c.a_hi, c.b_lo, mid) >= rem) ghi = mid;
+        if (cost_before(cm, c.a_lo, c.a_hi, c.b_lo, mid) >= rem) ghi = mid;
         else glo = mid + 1;
     }
     if (glo >= G) {
@@ -371,18 +413,21 @@ __device__ __forceinline__ long long find_start(const ClipCost* __restrict__ cos
         return __ldg(&cost[lo + 1].cum);
     }
     g_out = glo;
-    return c.cum + cost_before(c.a_lo, c.a_hi, c.b_lo, glo);
+    return c.cum + cost_before(cm, c.a_lo, c.a_hi, c.b_lo, glo);
 }
 
-__device__ __forceinline__ void store_fill_rows(float* __restrict__ out, int row0, int T, int nmel, int lane, float fill) {
-#pragma unroll
-    for (int q = 0; q < kGroupFrames; ++q) {
-        if (row0 + q >= T) break;
-        float* row = out + static_cast<size_t>(row0 + q) * nmel;
-#pragma unroll
-        for (int i = 0; i < kMelSlots; ++i)
-            if (lane + 32 * i < nmel) __stcs(row + lane + 32 * i, fill);
-    }
+// `count` floats starting at `ptr` := v, by the whole warp (16-byte stores once aligned)
+__device__ __forceinline__ void warp_fill(float* __restrict__ ptr, long long count, float v, int lane) {
+    const int head = static_cast<int>((16 - (reinterpret_cast<size_t>(ptr) & 15)) & 15) >> 2;
+    if (lane < head && lane < count) __stcs(ptr + lane, v);
+    if (count <= head) return;
+    ptr += head;
+    count -= head;
+    const long long n4 = count >> 2;
+    const float4 v4 = make_float4(v, v, v, v);
+    for (long long i = lane; i < n4; i += 32) __stcs(reinterpret_cast<float4*>(ptr) + i, v4);
+    const int tail = static_cast<int>(count & 3);
+    if (lane < tail) __stcs(ptr + 4 * n4 + lane, v);
 }
 
 // load a clip's descriptor, derive its conditioning constants, park everything in the warp's clip-state words
@@ -427,24 +472,12 @@ __device__ __forceinline__ void enter_clip(const StreamParams& p, int b, int lan
     }
     __syncwarp();
     if (lane == 0) {
-        cs[CS_N1] = d.n1;
-        cs[CS_NMIN] = nmin;
-        cs[CS_L1] = __float_as_int(d.l1);
-        cs[CS_L2] = __float_as_int(d.l2);
-        cs[CS_SUB1] = __float_as_int(sub1);
-        cs[CS_MEAN2] = __float_as_int(mean2);
-        cs[CS_MIXMEAN] = __float_as_int(mixmean);
-        cs[CS_FLAGS] = (d.flags & (kFlagAligned1 | kFlagAligned2)) | (mix ? kCsMix : 0);
-        cs[CS_F0] = d.f0;
-        cs[CS_F1] = d.f1;
-        cs[CS_T0] = d.t0;
-        cs[CS_T1] = d.t1;
-        cs[CS_MEFF] = d.m_eff;
-        cs[CS_ALO] = cc.a_lo;
-        cs[CS_AHI] = cc.a_hi;
-        cs[CS_BLO] = cc.b_lo;
-        *reinterpret_cast<long long*>(cs + CS_OFF1) = d.off1;
-        *reinterpret_cast<long long*>(cs + CS_OFF2) = d.off2;
+        cs_set_q(cs, CS_N1, d.n1, nmin, __float_as_int(d.l1), __float_as_int(d.l2));
+        cs_set_q(cs, CS_SUB1, __float_as_int(sub1), __float_as_int(mean2), __float_as_int(mixmean),
+                 (d.flags & (kFlagAligned1 | kFlagAligned2)) | (mix ? kCsMix : 0));
+        cs_set_q(cs, CS_OFF1, static_cast<int>(d.off1), static_cast<int>(d.off1 >> 32), static_cast<int>(d.off2), static_cast<int>(d.off2 >> 32));
+        cs_set_q(cs, CS_F0, d.f0, d.f1, d.t0, d.t1);
+        cs_set_q(cs, CS_MEFF, d.m_eff, cc.a_lo, cc.a_hi, cc.b_lo);
     }
     __syncwarp();
 }
@@ -460,7 +493,8 @@ __device__ __forceinline__ void epilogue(const StreamParams& p, const int* cs, c
     const float eps = 1.1920928955078125e-07f;  // kaldi.py:22
     const float fill = p.fill, floor_val = p.floor_val, la = p.log_scale, lb = p.log_bias;
     const int nmel = p.nmel;
-    const int mf0 = cs_i(cs, CS_F0), mf1 = cs_i(cs, CS_F1), t0 = cs_i(cs, CS_T0), t1 = cs_i(cs, CS_T1), m_eff = cs_i(cs, CS_MEFF);
+    const int4 mq = cs_q(cs, CS_F0);
+    const int mf0 = mq.x, mf1 = mq.y, t0 = mq.z, t1 = mq.w, m_eff = cs_i(cs, CS_MEFF);
     int mbin[kMelSlots];
     bool keep[kMelSlots];  // column survives the frequency mask
 #pragma unroll
@@ -513,6 +547,7 @@ __device__ __forceinline__ void trace_begin(int* cs, int lane) {
         cs[CS_TR_LIVE] = 0;
         cs[CS_TR_DEAD] = 0;
         cs[CS_TR_COLD] = 0;
+        cs[CS_TR_STEP] = 0;
     }
     __syncwarp();
 }
@@ -524,12 +559,24 @@ __device__ __forceinline__ void trace_mark(int* cs, int lane) {  // end of the p
     }
     __syncwarp();
 }
-__device__ __forceinline__ void trace_count(int* cs, int lane, int word) {
-    if (lane == 0) *reinterpret_cast<volatile int*>(cs + word) = cs_i(cs, word) + 1;
+__device__ __forceinline__ void trace_count(const StreamParams& p, int* cs, int lane, int word, int n) {
+    if (lane == 0) {
+        const int warp = threadIdx.x >> 5;
+        const int step = cs_i(cs, CS_TR_STEP);
+        *reinterpret_cast<volatile int*>(cs + CS_TR_STEP) = step + 1;
+        if (step < kTraceSteps) {
+            const long long c0 = cs_ll(cs, CS_TR_C0) & ((1ll << 40) - 1);
+            const long long kind = word == CS_TR_LIVE ? 1 : (word == CS_TR_COLD ? 2 : 3);
+            p.trace[(static_cast<size_t>(blockIdx.x) * kWarpsPerCta + warp) * kTraceWords + 4 + step] =
+                ((clock64() - c0) & ((1ll << 40) - 1)) | (kind << 40) | (static_cast<long long>(n) << 44);
+        }
+        *reinterpret_cast<volatile int*>(cs + word) = cs_i(cs, word) + n;
+    }
 }
-__device__ __forceinline__ void trace_end(const StreamParams& p, const int* cs, int lane, int warp) {
+__device__ __forceinline__ void trace_end(const StreamParams& p, const int* cs, int lane) {
     __syncwarp();
     if (lane == 0) {
+        const int warp = threadIdx.x >> 5;
         const long long packed = cs_ll(cs, CS_TR_C0);
         const long long c0 = packed & ((1ll << 40) - 1), pro = static_cast<unsigned long long>(packed) >> 40;
         const long long total = (clock64() - c0) & ((1ll << 40) - 1);
@@ -582,10 +629,11 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
     __syncwarp();
     constexpr int NIT = StageGeom<kOverlapSamples>::kIters;
     float4 ra[NIT], rc[NIT];
-    const int next = cs_i(cs, CS_NEXT);
+    const int4 ls = cs_q(cs, CS_B);  // b, g, budget, next
+    const int next = ls.w;
     if (next & kNextLive) {  // prefetch the next group's 640 new samples; they are consumed after the epilogue
         const MixState m = load_mix(cs, p.wav);
-        const int S1 = (cs_i(cs, CS_G) + 1) * kStepSamples;
+        const int S1 = (ls.y + 1) * kStepSamples;
         if (next & kNextFull) stage_issue<kOverlapSamples, true>(m, S1, lane, ra, rc);
         else stage_issue<kOverlapSamples, false>(m, S1, lane, ra, rc);
     }
@@ -599,8 +647,9 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
         warp_mel<MELSPEC>(lane, EX, mt, acc);
     }
     {
-        const int f0 = cs_i(cs, CS_G) * kGroupFrames;
-        float* out = p.out + static_cast<size_t>(cs_i(cs, CS_B)) * p.T * p.nmel;
+        const int4 l2 = cs_q(cs, CS_B);
+        const int f0 = l2.y * kGroupFrames;
+        float* out = p.out + static_cast<size_t>(l2.x) * p.T * p.nmel;
         const int* mel_bin = reinterpret_cast<const int*>(TAB + kTabMelBin);
         // MELSPEC is only selected for 128 mel bins: every (slot, lane) then owns a column
         if (p.fast_log) epilogue<true, MELSPEC>(p, cs, mel_bin, lane, f0, out, acc);
@@ -628,77 +677,90 @@ __global__ void __launch_bounds__(kThreads, 1) fbank_stream_kernel(const StreamP
     float* TAB = smem;
     float* WS = smem + p.tab_floats + warp * kWarpFloats;
     int* cs = reinterpret_cast<int*>(WS + kWsCS);
+    // ---- prologue: the table copy and the partition search overlap (both are round trips to L2) ----
+    const int n4 = p.tab_floats / 4;
+    const float4* tsrc = reinterpret_cast<const float4*>(p.tab);
+    float4 tv = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (tid < n4) tv = __ldg(tsrc + tid);
+    if (p.trace) trace_begin(cs, lane);
+    // this warp's share of the work
+    const long long W = static_cast<long long>(gridDim.x) * kWarpsPerCta;
+    const long long r = static_cast<long long>(warp) * gridDim.x + blockIdx.x;  // neighbouring ranges on different SMs
+    const long long c_lo = p.total_cost * r / W, c_hi = p.total_cost * (r + 1) / W;
+    const bool has_work = c_lo < c_hi;
+    if (has_work) {
+        int b, g;
+        const long long start_cost = find_start(p.cost, p.cm, p.n_clips, p.G, c_lo, lane, b, g);
+        // groups are taken while the cost consumed is < budget
+        if (lane == 0) cs_set_q(cs, CS_B, b, g, static_cast<int>(c_hi - start_cost), 0);
+    }
     {
-        const float4* src = reinterpret_cast<const float4*>(p.tab);
         float4* dst = reinterpret_cast<float4*>(TAB);
-        for (int i = tid; i < p.tab_floats / 4; i += kThreads) dst[i] = __ldg(src + i);
+        if (tid < n4) dst[tid] = tv;
+        for (int i = tid + kThreads; i < n4; i += kThreads) dst[i] = __ldg(tsrc + i);
     }
     __syncthreads();
-
-    if (p.trace) trace_begin(cs, lane);
-    // ---- this warp's share of the work ----
-    {
-        const long long W = static_cast<long long>(gridDim.x) * kWarpsPerCta;
-        const long long r = static_cast<long long>(warp) * gridDim.x + blockIdx.x;  // neighbouring ranges on different SMs
-        const long long c_lo = p.total_cost * r / W, c_hi = p.total_cost * (r + 1) / W;
-        if (c_lo >= c_hi) {
-            if (p.trace) trace_end(p, cs, lane, warp);
-            return;
-        }
-        int b, g;
-        const long long start_cost = find_start(p.cost, p.n_clips, p.G, c_lo, b, g);
-        cs_set(cs, CS_B, b, lane);
-        cs_set(cs, CS_G, g, lane);
-        cs_set(cs, CS_BUDGET, static_cast<int>(c_hi - start_cost), lane);  // groups are taken while the cost consumed is < budget
-        __syncwarp();
+    if (!has_work) {
+        if (p.trace) trace_end(p, cs, lane);
+        return;
     }
     int loaded_b = -1;
     bool staged = false;  // the window holds the samples of the current group
     if (p.trace) trace_mark(cs, lane);
 
     while (true) {
-        const int b = cs_i(cs, CS_B), g = cs_i(cs, CS_G);
-        int budget = cs_i(cs, CS_BUDGET);
+        const int4 ls = cs_q(cs, CS_B);
+        const int b = ls.x, g = ls.y;
+        int budget = ls.z;
         if (b >= p.n_clips || budget <= 0) break;
         if (b != loaded_b) {
             enter_clip<EXACT>(p, b, lane, cs);
             loaded_b = b;
             staged = false;
         }
-        const int f0 = kGroupFrames * g;
-        const bool dead = group_dead(cs, g);
-        bool next_live = false;
-        if (p.trace) trace_count(cs, lane, dead ? CS_TR_DEAD : (staged ? CS_TR_LIVE : CS_TR_COLD));
-        if (dead) {
-            store_fill_rows(p.out + static_cast<size_t>(b) * p.T * p.nmel, f0, p.T, p.nmel, lane, p.fill);
-            budget -= 1;
-        } else {
+        const int4 dq = cs_q(cs, CS_MEFF);  // m_eff, a_lo, a_hi, b_lo
+        if (is_dead(dq.y, dq.z, dq.w, g)) {
+            // a run of constant rows: take as many of its groups as the budget covers, one contiguous fill
+            const int run_end = (g >= dq.w) ? p.G : dq.z;
+            const int n = min(run_end - g, (budget + p.cm.dead - 1) / p.cm.dead);
+            if (p.trace) trace_count(p, cs, lane, CS_TR_DEAD, n);
+            const int row0 = kGroupFrames * g, row1 = min(p.T, kGroupFrames * (g + n));
+            warp_fill(p.out + (static_cast<size_t>(b) * p.T + row0) * p.nmel, static_cast<long long>(row1 - row0) * p.nmel, p.fill, lane);
+            const bool wrap = g + n == p.G;
+            if (lane == 0) cs_set_q(cs, CS_B, wrap ? b + 1 : b, wrap ? 0 : g + n, budget - n * p.cm.dead, 0);
+            staged = false;
+            __syncwarp();
+            continue;
+        }
+        if (p.trace) trace_count(p, cs, lane, staged ? CS_TR_LIVE : CS_TR_COLD, 1);
+        bool next_live;
+        {
             const MixState m = load_mix(cs, p.wav);
             if (!staged) {  // cold start of a run of groups
                 constexpr int NIT0 = StageGeom<0>::kIters;
                 float4 ra[NIT0], rc[NIT0];
                 float carry = 0.f;
-                stage_issue<0, false>(m, f0 * kFrameShift, lane, ra, rc);
-                stage_commit<EXACT, 0, false>(m, f0 * kFrameShift, lane, p.preemph, p.c1, ra, rc, WS + kWsD, WS + kWsBS, WS + kWsXS, carry);
+                const int S0 = g * kStepSamples;
+                stage_issue<0, false>(m, S0, lane, ra, rc);
+                stage_commit<EXACT, 0, false>(m, S0, lane, p.preemph, p.c1, ra, rc, WS + kWsD, WS + kWsBS, WS + kWsXS, carry);
                 cs_set(cs, CS_CARRY, __float_as_int(carry), lane);
             }
-            budget -= kLiveCost;
-            next_live = (g + 1 < p.G) && !group_dead(cs, g + 1) && budget > 0;
+            budget -= p.cm.live + (run_start(dq.y, dq.z, g) ? p.cm.cold : 0);
+            next_live = (g + 1 < p.G) && !is_dead(dq.y, dq.z, dq.w, g + 1) && budget > 0;
             const bool full_next = next_live && window_full(m, (g + 1) * kStepSamples);
-            cs_set(cs, CS_NEXT, (next_live ? kNextLive : 0) | (full_next ? kNextFull : 0), lane);
+            if (lane == 0) cs_set_q(cs, CS_B, b, g, budget, (next_live ? kNextLive : 0) | (full_next ? kNextFull : 0));
         }
-        cs_set(cs, CS_BUDGET, budget, lane);
         __syncwarp();
-        if (!dead) process_group<EXACT, MELSPEC>(p, TAB, WS, lane);
+        process_group<EXACT, MELSPEC>(p, TAB, WS, lane);
         staged = next_live;
-        // advance (CS_B / CS_G are read by process_group, so they move only now)
-        const int g1 = cs_i(cs, CS_G) + 1;
-        const bool wrap = g1 == p.G;
-        cs_set(cs, CS_G, wrap ? 0 : g1, lane);
-        if (wrap) cs_set(cs, CS_B, cs_i(cs, CS_B) + 1, lane);
+        {  // advance (CS_B / CS_G are read by process_group, so they move only now)
+            const int4 l2 = cs_q(cs, CS_B);
+            const bool wrap = l2.y + 1 == p.G;
+            if (lane == 0) cs_set_q(cs, CS_B, wrap ? l2.x + 1 : l2.x, wrap ? 0 : l2.y + 1, l2.z, 0);
+        }
         __syncwarp();
     }
-    if (p.trace) trace_end(p, cs, lane, warp);
+    if (p.trace) trace_end(p, cs, lane);
 }
 
 }  // namespace psla

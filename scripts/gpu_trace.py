@@ -43,6 +43,26 @@ def main():
     for k in range(20):
         fe.forward_packed(sets[k % 4], src1, src2, lam, masks, out=outs[k % 4])
     torch.cuda.synchronize()
+    def time_steps(n=200):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for k in range(10):
+            fe.forward_packed(sets[k % 4], src1, src2, lam, masks, out=outs[k % 4])
+        e0.record()
+        for k in range(n):
+            fe.forward_packed(sets[k % 4], src1, src2, lam, masks, out=outs[k % 4])
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) * 1e3 / n
+
+    ref = outs[0].clone()
+    for cm in [(64, 2, 48), (64, 2, 0), (64, 4, 48), (64, 1, 48), (64, 2, 32), (64, 2, 64), (64, 8, 48), (32, 1, 0)]:
+        fe.set_cost_model(*cm)
+        us = time_steps()
+        fe.forward_packed(sets[0], src1, src2, lam, masks, out=outs[0])
+        torch.cuda.synchronize()
+        print(f"cost model live/dead/cold {cm}: {us:.2f} us/step; output identical: {bool(torch.equal(ref, outs[0]))}")
+    fe.set_cost_model(64, 2, 48)
+
     tr = fe.set_trace(True)
     recs = []
     for k in range(8):
@@ -55,7 +75,7 @@ def main():
     fe.set_trace(False)
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     np.savez(os.path.join(ROOT, "gpurun_out", "trace.npz"), us=np.array([r[0] for r in recs]), rec=np.stack([r[1] for r in recs]))
-    for us, r in recs[-3:]:
+    for us, r in recs[-2:]:
         t0, t1 = r[:, 0], r[:, 1]
         pro = r[:, 2] & 0xFFFFFFFF
         tot = (r[:, 2] >> 32) & 0xFFFFFFFF
@@ -69,24 +89,37 @@ def main():
         print("percentiles            min        p5       p25       p50       p75       p95       max")
         print("start  (us)     ", pct((t0[ok] - base) / 1e3))
         print("end    (us)     ", pct((t1[ok] - base) / 1e3))
-        print("dur    (us)     ", pct((t1[ok] - t0[ok]) / 1e3))
         print("prologue cycles ", pct(pro[ok]))
         print("total cycles    ", pct(tot[ok]))
         print("live groups     ", pct(live[ok]))
         print("dead groups     ", pct(dead[ok]))
         print("cold starts     ", pct(cold[ok]))
-        work = (tot[ok] - pro[ok]) / np.maximum(live[ok], 1)
-        print("cycles/live grp ", pct(work))
-        # per SM: last warp end, sum of live groups
+        # per-step durations by kind and by position in the warp's sequence
+        steps = r[:, 4:]
+        cyc = steps & ((1 << 40) - 1)
+        kind = (steps >> 40) & 0xF
+        ngrp = (steps >> 44) & 0xFFFF
+        nxt = np.concatenate([cyc[:, 1:], np.zeros((len(cyc), 1), dtype=cyc.dtype)], axis=1)
+        valid_next = np.concatenate([kind[:, 1:] > 0, np.zeros((len(cyc), 1), dtype=bool)], axis=1)
+        last = (kind > 0) & ~valid_next
+        dur = np.where(valid_next, nxt - cyc, 0)
+        dur = np.where(last, tot[:, None] - cyc, dur)  # the last step ends with the warp
+        for kk, name in ((1, "live"), (2, "cold+live"), (3, "dead run")):
+            m = (kind == kk) & ok[:, None]
+            if m.any():
+                d = dur[m]
+                print(f"step cycles {name:10s}", pct(d), f"  n={m.sum()}  groups/step {ngrp[m].mean():.1f}")
+        for pos in range(0, 12):
+            m = (kind[:, pos] == 1) & ok
+            if m.any():
+                print(f"  live step at position {pos:2d}: median {np.median(dur[m, pos]):8.0f} cycles  start at {np.median(cyc[m, pos]):8.0f}")
         sm_end = {}
-        for s, e, lv in zip(smid[ok], t1[ok], live[ok]):
-            a = sm_end.setdefault(int(s), [0, 0])
-            a[0] = max(a[0], (e - base) / 1e3)
-            a[1] += int(lv)
+        for s_, e, lv in zip(smid[ok], t1[ok], live[ok]):
+            a_ = sm_end.setdefault(int(s_), [0, 0])
+            a_[0] = max(a_[0], (e - base) / 1e3)
+            a_[1] += int(lv)
         ends = np.array([v[0] for v in sm_end.values()])
-        lives = np.array([v[1] for v in sm_end.values()])
         print("SM end (us)     ", pct(ends))
-        print("SM live groups  ", pct(lives))
         ghz = (tot[ok] / np.maximum(t1[ok] - t0[ok], 1)).mean()
         print(f"mean clock {ghz:.3f} GHz; total live groups {live[ok].sum()}, dead {dead[ok].sum()}")
 

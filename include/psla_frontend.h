@@ -108,16 +108,18 @@ int psla_frontend_set_timing(psla_frontend_t* handle, int enable);
 int psla_frontend_get_timing(psla_frontend_t* handle, double* stats_ms, double* tile_ms, int64_t* n_forward);
 
 /* Optional per-warp timeline of the streaming kernel (tracing aid; the reference has no counterpart).  While a DEVICE
- * buffer of psla_frontend_trace_records() records x 4 int64 is installed, every warp of every forward() writes 8
- * consecutive records (32 int64):
+ * buffer of psla_frontend_trace_records() records (one per warp) x psla_frontend_trace_words() int64 is installed,
+ * every warp of every forward() writes
  *   [0] globaltimer ns at warp start   [1] globaltimer ns at warp end
  *   [2] cycles before its first group | total cycles << 32
  *   [3] smid | groups computed << 16 | constant (masked / padded) groups << 32 | cold starts << 48
- *   [4 + i], i < 28: i-th loop step: cycles since warp start | kind << 40 (1 computed group, 2 computed group that
- *            staged its whole window, 3 run of constant groups) | groups in the step << 44
+ *   [4 + i]: i-th event: cycles since warp start | kind << 40 | groups in the step << 44; kinds 1..3 open a loop step
+ *            (1 computed group, 2 computed group that staged its whole window, 3 run of constant groups), 4..9 mark
+ *            phases inside it (4 clip entered, 5 window staged, 6 pass 1, 7 pass 2 + power, 8 mel, 9 epilogue done)
  * Pass NULL to switch it off. */
 int psla_frontend_set_trace(psla_frontend_t* handle, int64_t* device_buf, size_t capacity_records);
 int psla_frontend_trace_records(const psla_frontend_t* handle);
+int psla_frontend_trace_words(void);
 
 /* Weights of the work partition between the warps of the streaming kernel (performance tuning only; results do not
  * depend on them): cost of a computed group of 4 rows, of a group of 4 constant rows, and the surcharge of the first

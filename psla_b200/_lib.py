@@ -37,6 +37,7 @@ SYMBOLS = {
     "psla_frontend_get_timing": (c_int, [c_void_p, POINTER(c_double), POINTER(c_double), POINTER(c_int64)]),
     "psla_frontend_set_trace": (c_int, [c_void_p, c_void_p, c_size_t]),
     "psla_frontend_trace_records": (c_int, [c_void_p]),
+    "psla_frontend_trace_words": (c_int, []),
     "psla_frontend_set_cost_model": (c_int, [c_void_p, c_int, c_int, c_int]),
     "psla_strerror": (c_char_p, [c_int]),
     "psla_last_cuda_error": (c_int, [c_void_p]),

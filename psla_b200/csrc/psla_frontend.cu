@@ -283,7 +283,7 @@ int psla_frontend_get_timing(psla_frontend_t* h, double* stats_ms, double* tile_
 
 int psla_frontend_set_trace(psla_frontend_t* h, int64_t* device_buf, size_t capacity_records) {
     if (!h) return PSLA_E_INVALID;
-    const size_t need = static_cast<size_t>(h->num_sms > 0 ? h->num_sms : 148) * kWarpsPerCta * (kTraceWords / 4);
+    const size_t need = static_cast<size_t>(h->num_sms > 0 ? h->num_sms : 148) * kWarpsPerCta;
     if (device_buf && capacity_records < need) return PSLA_E_WORKSPACE;
     static_assert(sizeof(long long) == sizeof(int64_t), "trace word");
     h->trace = reinterpret_cast<long long*>(device_buf);
@@ -291,8 +291,10 @@ int psla_frontend_set_trace(psla_frontend_t* h, int64_t* device_buf, size_t capa
 }
 
 int psla_frontend_trace_records(const psla_frontend_t* h) {
-    return h ? (h->num_sms > 0 ? h->num_sms : 148) * kWarpsPerCta * (kTraceWords / 4) : 0;
+    return h ? (h->num_sms > 0 ? h->num_sms : 148) * kWarpsPerCta : 0;
 }
+
+int psla_frontend_trace_words(void) { return kTraceWords; }
 
 int psla_frontend_set_cost_model(psla_frontend_t* h, int live, int dead, int cold) {
     // total cost of a batch must stay well inside int64 and a warp's budget inside int32

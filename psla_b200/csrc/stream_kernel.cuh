@@ -69,8 +69,9 @@ struct StreamParams {
 };
 // words per warp: [0] globaltimer at warp start (ns)  [1] at warp end  [2] clock64 cycles before the first group | total << 32
 // [3] smid | live groups << 16 | dead groups << 32 | cold starts << 48  [4 + i] i-th loop step of the warp (i < kTraceSteps):
-// cycles since warp start | kind << 40 (1 live, 2 cold-started live, 3 run of dead groups) | groups in the step << 44
-constexpr int kTraceSteps = 28;
+// cycles since warp start | kind << 40 (1 live, 2 cold-started live, 3 run of dead groups; 4.. phase markers inside a step:
+// 4 clip entered, 5 cold window staged, 6 pass 1 done, 7 pass 2 + power done, 8 mel done, 9 epilogue done, 10 cold loads issued, 11 prefetch issued) | groups << 44
+constexpr int kTraceSteps = 124;
 constexpr int kTraceWords = 4 + kTraceSteps;
 
 __device__ __forceinline__ ClipDesc load_desc(const ClipDesc* __restrict__ p) {
@@ -277,28 +278,31 @@ __device__ __forceinline__ float mix_sample(const MixState& m, float a, float c,
 }
 
 // ------------------------------------------------------------------------------------------------
-// Warp-private staging of the group window.  U0 = first window sample staged (0: cold start, 7 float4 per lane;
-// 240: steady state, 5 float4 per lane).  issue() only loads (so the latency can hide behind the mel / epilogue of the
-// previous group), commit() conditions the samples and writes
+// Warp-private staging of window samples [U0, U1) of the group window ([0, 240): the part a group shares with its
+// predecessor, only staged on a cold start; [240, 880): the 640 new samples of every step).  issue() only loads (so the
+// latency can hide behind the mel / epilogue of the previous group), commit() conditions the samples and writes
 //   D[dpad(u)] = x[u] - p*x[u-1],  BS[u/16] = sum of 16 samples,  XS[u/160] = (1-p)*x[u]  (u % 160 == 0).
 // `carry` is x of the last sample staged so far (pre-emphasis neighbour of the next staged sample).
 // ------------------------------------------------------------------------------------------------
-template <int U0>
+template <int U0, int U1>
 struct StageGeom {
-    static constexpr int kFloat4 = (kGroupSamples - U0) / 4;  // 220 or 160
-    static constexpr int kIters = (kFloat4 + 31) / 32;        // 7 or 5
-    static constexpr int kLastLane = (kFloat4 - 1) % 32;      // lane holding the window's last float4
+    static_assert(U0 % 16 == 0 && U1 % 16 == 0 && U0 < U1, "whole 16-sample blocks");
+    static constexpr int kFloat4 = (U1 - U0) / 4;         // 60 or 160
+    static constexpr int kIters = (kFloat4 + 31) / 32;    // 2 or 5
+    static constexpr int kLastLane = (kFloat4 - 1) % 32;  // lane holding the range's last float4
 };
 
-template <int U0, bool FULL, int NIT>
+template <int U0, int U1, bool FULL, int NIT>
 __device__ __forceinline__ void stage_issue(const MixState& m, int S0, int lane, float4 (&a)[NIT], float4 (&c)[NIT]) {
+    using Geo = StageGeom<U0, U1>;
+    static_assert(NIT >= Geo::kIters, "register arrays too small");
 #pragma unroll
-    for (int it = 0; it < NIT; ++it) {
+    for (int it = 0; it < Geo::kIters; ++it) {
         const int L = lane + 32 * it;
         const int s = S0 + U0 + 4 * L;
         a[it] = make_float4(0.f, 0.f, 0.f, 0.f);
         c[it] = a[it];
-        if ((it + 1) * 32 <= StageGeom<U0>::kFloat4 || L < StageGeom<U0>::kFloat4) {
+        if ((it + 1) * 32 <= Geo::kFloat4 || L < Geo::kFloat4) {
             if (FULL) {
                 a[it] = __ldg(reinterpret_cast<const float4*>(m.w1 + s));
                 if (m.mix) c[it] = __ldg(reinterpret_cast<const float4*>(m.w2 + s));
@@ -310,17 +314,18 @@ __device__ __forceinline__ void stage_issue(const MixState& m, int S0, int lane,
     }
 }
 
-template <bool EXACT, int U0, bool FULL, int NIT>
+template <bool EXACT, int U0, int U1, bool FULL, int NIT>
 __device__ __forceinline__ void stage_commit(const MixState& m, int S0, int lane, float pe, float c1, const float4 (&a)[NIT],
                                              const float4 (&c)[NIT], float* __restrict__ D, float* __restrict__ BS,
                                              float* __restrict__ XS, float& carry) {
+    using Geo = StageGeom<U0, U1>;
     float last_w = 0.f;
 #pragma unroll
-    for (int it = 0; it < NIT; ++it) {
+    for (int it = 0; it < Geo::kIters; ++it) {
         const int L = lane + 32 * it;
         const int u = U0 + 4 * L;
         const int s = S0 + u;
-        const bool in = ((it + 1) * 32 <= StageGeom<U0>::kFloat4) || L < StageGeom<U0>::kFloat4;
+        const bool in = ((it + 1) * 32 <= Geo::kFloat4) || L < Geo::kFloat4;
         float4 x;
         x.x = mix_sample<EXACT, FULL>(m, a[it].x, c[it].x, s);
         x.y = mix_sample<EXACT, FULL>(m, a[it].y, c[it].y, s + 1);
@@ -346,7 +351,7 @@ __device__ __forceinline__ void stage_commit(const MixState& m, int S0, int lane
             if (U0 / 4 + L == 40 * q) XS[q] = c1 * x.x;
         }
     }
-    if (StageGeom<U0>::kLastLane != 31) carry = __shfl_sync(0xffffffffu, last_w, StageGeom<U0>::kLastLane);
+    if (Geo::kLastLane != 31) carry = __shfl_sync(0xffffffffu, last_w, Geo::kLastLane);
 }
 
 // the 240 samples (and their block sums / frame-start values) the next group shares with this one move to the front
@@ -466,10 +471,7 @@ __device__ __forceinline__ void enter_clip(const StreamParams& p, int b, int lan
             }
         }
     }
-    if (!EXACT) {
-        const float a0 = __ldg(p.wav + d.off1);
-        sub1 = mix ? fmaf(d.l1, a0, d.l2 * __ldg(p.wav + d.off2)) : a0;
-    }
+    // (fused mode: CS_SUB1 is filled by the first cold start of the clip, whose loads fetch the first samples anyway)
     __syncwarp();
     if (lane == 0) {
         cs_set_q(cs, CS_N1, d.n1, nmin, __float_as_int(d.l1), __float_as_int(d.l2));
@@ -487,22 +489,31 @@ __device__ __forceinline__ void enter_clip(const StreamParams& p, int b, int lan
 //             ~1e-6 in log-mel units); cells on the float-epsilon floor take the host-computed IEEE constant, so they
 //             stay bit-identical to the reference.
 //   !FASTLOG  logf + IEEE subtraction / division, the reference's expression verbatim.
-template <bool FASTLOG, bool ALLBINS>
+//   NMEL      compile-time row length (every (slot, lane) then owns a column and row offsets are immediates); 0: p.nmel
+__device__ __forceinline__ float lg2_ftz(float x) {  // one MUFU.LG2: the argument is >= eps, never subnormal
+    float y;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+template <bool FASTLOG, int NMEL>
 __device__ __forceinline__ void epilogue(const StreamParams& p, const int* cs, const int* mel_bin, int lane, int f0, float* __restrict__ out,
                                          const float (&acc)[kMelSlots][kGroupFrames]) {
     const float eps = 1.1920928955078125e-07f;  // kaldi.py:22
     const float fill = p.fill, floor_val = p.floor_val, la = p.log_scale, lb = p.log_bias;
-    const int nmel = p.nmel;
+    const int nmel = NMEL ? NMEL : p.nmel;
     const int4 mq = cs_q(cs, CS_F0);
     const int mf0 = mq.x, mf1 = mq.y, t0 = mq.z, t1 = mq.w, m_eff = cs_i(cs, CS_MEFF);
-    int mbin[kMelSlots];
-    bool keep[kMelSlots];  // column survives the frequency mask
+    float* col[kMelSlots];  // the lane's four columns at row f0
+    bool keep[kMelSlots];   // column survives the frequency mask
+    bool own[kMelSlots];
 #pragma unroll
     for (int i = 0; i < kMelSlots; ++i) {
-        mbin[i] = mel_bin[32 * i + lane];
-        keep[i] = !(mbin[i] >= mf0 && mbin[i] < mf1);
+        const int mb = mel_bin[32 * i + lane];
+        own[i] = NMEL != 0 || mb >= 0;
+        keep[i] = !(mb >= mf0 && mb < mf1);
+        col[i] = out + static_cast<size_t>(f0) * nmel + max(mb, 0);
     }
-    float* orow = out + static_cast<size_t>(f0) * nmel;
     const int rows = min(kGroupFrames, p.T - f0);
 #pragma unroll
     for (int q = 0; q < kGroupFrames; ++q) {
@@ -514,17 +525,16 @@ __device__ __forceinline__ void epilogue(const StreamParams& p, const int* cs, c
                 const float e = acc[i][q];
                 float v;
                 if (FASTLOG) {  // branch-free: the log of a floored / dead cell is computed and discarded
-                    v = fmaf(__log2f(fmaxf(e, eps)), la, lb);
+                    v = fmaf(lg2_ftz(fmaxf(e, eps)), la, lb);
                     v = (e > eps) ? v : floor_val;
                 } else {
                     const float lg = logf(fmaxf(e, eps));
                     v = p.skip_norm ? lg : __fdiv_rn(__fsub_rn(lg, p.norm_mean), p.norm_div);
                 }
                 v = (rlive && keep[i]) ? v : fill;
-                if (ALLBINS || mbin[i] >= 0) __stcs(orow + mbin[i], v);
+                if (own[i]) __stcs(col[i] + q * nmel, v);
             }
         }
-        orow += nmel;
     }
 }
 
@@ -573,6 +583,18 @@ __device__ __forceinline__ void trace_count(const StreamParams& p, int* cs, int 
         *reinterpret_cast<volatile int*>(cs + word) = cs_i(cs, word) + n;
     }
 }
+__device__ __forceinline__ void trace_phase(const StreamParams& p, int* cs, int lane, int kind) {
+    __syncwarp();
+    if (lane == 0) {
+        const int step = cs_i(cs, CS_TR_STEP);
+        if (step < kTraceSteps) {
+            *reinterpret_cast<volatile int*>(cs + CS_TR_STEP) = step + 1;
+            const long long c0 = cs_ll(cs, CS_TR_C0) & ((1ll << 40) - 1);
+            p.trace[(static_cast<size_t>(blockIdx.x) * kWarpsPerCta + (threadIdx.x >> 5)) * kTraceWords + 4 + step] =
+                ((clock64() - c0) & ((1ll << 40) - 1)) | (static_cast<long long>(kind) << 40);
+        }
+    }
+}
 __device__ __forceinline__ void trace_end(const StreamParams& p, const int* cs, int lane) {
     __syncwarp();
     if (lane == 0) {
@@ -591,10 +613,14 @@ __device__ __forceinline__ void trace_end(const StreamParams& p, const int* cs, 
     }
 }
 
-// one live group: frame means, pass 1, (shift), pass 2, power, (prefetch), mel, epilogue, (commit).
-// Everything it needs beyond the kernel parameters comes from the warp's shared-memory state (CS_*).
-template <bool EXACT, bool MELSPEC>
-__device__ __forceinline__ void process_group(const StreamParams& p, const float* TAB, float* WS, int lane) {
+constexpr int kStageIters = StageGeom<kOverlapSamples, kGroupSamples>::kIters;  // float4 per lane and waveform of one step
+
+// one live group whose window is staged: frame means, pass 1, (shift), pass 2, power, (prefetch), mel, epilogue.
+// Everything it needs beyond the kernel parameters comes from the warp's shared-memory state (CS_*).  The prefetch
+// leaves the next group's 640 new samples in ra / rc; the caller commits them at the top of its next step.
+template <bool MELSPEC>
+__device__ __forceinline__ void process_group(const StreamParams& p, const float* TAB, float* WS, int lane, float4 (&ra)[kStageIters],
+                                              float4 (&rc)[kStageIters]) {
     float* D = WS + kWsD;
     float* BS = WS + kWsBS;
     float* XS = WS + kWsXS;
@@ -617,6 +643,7 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
     }
     pair_pass1(n2, h, D, XS, TAB + kTabWin, TAB + kTabTwz, EX + h * kExSecondPair, cmu_x, cmu_y);
     __syncwarp();
+    if (p.trace) trace_phase(p, cs, lane, 6);
     if (cs_i(cs, CS_NEXT) & kNextLive) stage_shift(lane, D, BS, XS);
     {
         // pass 2 re-maps the lanes: pair h2 = lane & 1, row t = lane >> 1 (see kExSecondPair)
@@ -627,15 +654,16 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
         pair_power_store(t, h2, ar, ai, br, bi, EX);
     }
     __syncwarp();
-    constexpr int NIT = StageGeom<kOverlapSamples>::kIters;
-    float4 ra[NIT], rc[NIT];
-    const int4 ls = cs_q(cs, CS_B);  // b, g, budget, next
-    const int next = ls.w;
-    if (next & kNextLive) {  // prefetch the next group's 640 new samples; they are consumed after the epilogue
-        const MixState m = load_mix(cs, p.wav);
-        const int S1 = (ls.y + 1) * kStepSamples;
-        if (next & kNextFull) stage_issue<kOverlapSamples, true>(m, S1, lane, ra, rc);
-        else stage_issue<kOverlapSamples, false>(m, S1, lane, ra, rc);
+    if (p.trace) trace_phase(p, cs, lane, 7);
+    {
+        const int4 ls = cs_q(cs, CS_B);  // b, g, budget, next
+        if (ls.w & kNextLive) {  // prefetch the next group's 640 new samples; they are consumed after the epilogue
+            const MixState m = load_mix(cs, p.wav);
+            const int S1 = (ls.y + 1) * kStepSamples;
+            if (ls.w & kNextFull) stage_issue<kOverlapSamples, kGroupSamples, true>(m, S1, lane, ra, rc);
+            else stage_issue<kOverlapSamples, kGroupSamples, false>(m, S1, lane, ra, rc);
+            if (p.trace) trace_phase(p, cs, lane, 11);
+        }
     }
     float acc[kMelSlots][kGroupFrames];
     {
@@ -646,24 +674,17 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
         mt.w = TAB + kTabMelW;
         warp_mel<MELSPEC>(lane, EX, mt, acc);
     }
+    if (p.trace) trace_phase(p, cs, lane, 8);
     {
         const int4 l2 = cs_q(cs, CS_B);
         const int f0 = l2.y * kGroupFrames;
         float* out = p.out + static_cast<size_t>(l2.x) * p.T * p.nmel;
         const int* mel_bin = reinterpret_cast<const int*>(TAB + kTabMelBin);
         // MELSPEC is only selected for 128 mel bins: every (slot, lane) then owns a column
-        if (p.fast_log) epilogue<true, MELSPEC>(p, cs, mel_bin, lane, f0, out, acc);
-        else epilogue<false, MELSPEC>(p, cs, mel_bin, lane, f0, out, acc);
+        if (p.fast_log) epilogue<true, MELSPEC ? kMaxMel : 0>(p, cs, mel_bin, lane, f0, out, acc);
+        else epilogue<false, MELSPEC ? kMaxMel : 0>(p, cs, mel_bin, lane, f0, out, acc);
     }
-    if (next & kNextLive) {
-        const MixState m = load_mix(cs, p.wav);
-        const int S1 = (cs_i(cs, CS_G) + 1) * kStepSamples;
-        float carry = cs_f(cs, CS_CARRY);
-        if (next & kNextFull) stage_commit<EXACT, kOverlapSamples, true>(m, S1, lane, p.preemph, p.c1, ra, rc, D, BS, XS, carry);
-        else stage_commit<EXACT, kOverlapSamples, false>(m, S1, lane, p.preemph, p.c1, ra, rc, D, BS, XS, carry);
-        cs_set(cs, CS_CARRY, __float_as_int(carry), lane);
-    }
-    __syncwarp();
+    if (p.trace) trace_phase(p, cs, lane, 9);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -705,7 +726,8 @@ __global__ void __launch_bounds__(kThreads, 1) fbank_stream_kernel(const StreamP
         return;
     }
     int loaded_b = -1;
-    bool staged = false;  // the window holds the samples of the current group
+    bool staged = false;  // the current group's overlap samples are in the window and its new samples in ra / rc
+    float4 ra[kStageIters], rc[kStageIters];
     if (p.trace) trace_mark(cs, lane);
 
     while (true) {
@@ -717,6 +739,7 @@ __global__ void __launch_bounds__(kThreads, 1) fbank_stream_kernel(const StreamP
             enter_clip<EXACT>(p, b, lane, cs);
             loaded_b = b;
             staged = false;
+            if (p.trace) trace_phase(p, cs, lane, 4);
         }
         const int4 dq = cs_q(cs, CS_MEFF);  // m_eff, a_lo, a_hi, b_lo
         if (is_dead(dq.y, dq.z, dq.w, g)) {
@@ -735,23 +758,52 @@ __global__ void __launch_bounds__(kThreads, 1) fbank_stream_kernel(const StreamP
         if (p.trace) trace_count(p, cs, lane, staged ? CS_TR_LIVE : CS_TR_COLD, 1);
         bool next_live;
         {
-            const MixState m = load_mix(cs, p.wav);
-            if (!staged) {  // cold start of a run of groups
-                constexpr int NIT0 = StageGeom<0>::kIters;
-                float4 ra[NIT0], rc[NIT0];
-                float carry = 0.f;
-                const int S0 = g * kStepSamples;
-                stage_issue<0, false>(m, S0, lane, ra, rc);
-                stage_commit<EXACT, 0, false>(m, S0, lane, p.preemph, p.c1, ra, rc, WS + kWsD, WS + kWsBS, WS + kWsXS, carry);
-                cs_set(cs, CS_CARRY, __float_as_int(carry), lane);
+            MixState m = load_mix(cs, p.wav);
+            const int S0 = g * kStepSamples;
+            const bool full = window_full(m, S0);
+            float* D = WS + kWsD;
+            float* BS = WS + kWsBS;
+            float* XS = WS + kWsXS;
+            float carry;
+            if (!staged) {  // cold start of a run of groups: the whole window is loaded here, nothing was prefetched
+                constexpr int NH = StageGeom<0, kOverlapSamples>::kIters;
+                float4 ha[NH], hc[NH];
+                float a0 = 0.f, c0 = 0.f;
+                if (!EXACT) {  // the constant removed from the clip (see mix_sample): its first sample(s)
+                    a0 = __ldg(m.w1);
+                    if (m.mix) c0 = __ldg(m.w2);
+                }
+                if (full) {
+                    stage_issue<0, kOverlapSamples, true>(m, S0, lane, ha, hc);
+                    stage_issue<kOverlapSamples, kGroupSamples, true>(m, S0, lane, ra, rc);
+                } else {
+                    stage_issue<0, kOverlapSamples, false>(m, S0, lane, ha, hc);
+                    stage_issue<kOverlapSamples, kGroupSamples, false>(m, S0, lane, ra, rc);
+                }
+                if (p.trace) trace_phase(p, cs, lane, 10);
+                if (!EXACT) {
+                    m.sub1 = m.mix ? fmaf(m.l1, a0, m.l2 * c0) : a0;
+                    cs_set(cs, CS_SUB1, __float_as_int(m.sub1), lane);
+                }
+                carry = 0.f;
+                if (full) stage_commit<EXACT, 0, kOverlapSamples, true>(m, S0, lane, p.preemph, p.c1, ha, hc, D, BS, XS, carry);
+                else stage_commit<EXACT, 0, kOverlapSamples, false>(m, S0, lane, p.preemph, p.c1, ha, hc, D, BS, XS, carry);
+            } else {
+                carry = cs_f(cs, CS_CARRY);
             }
+            if (full) stage_commit<EXACT, kOverlapSamples, kGroupSamples, true>(m, S0, lane, p.preemph, p.c1, ra, rc, D, BS, XS, carry);
+            else stage_commit<EXACT, kOverlapSamples, kGroupSamples, false>(m, S0, lane, p.preemph, p.c1, ra, rc, D, BS, XS, carry);
+            if (p.trace) trace_phase(p, cs, lane, 5);
             budget -= p.cm.live + (run_start(dq.y, dq.z, g) ? p.cm.cold : 0);
             next_live = (g + 1 < p.G) && !is_dead(dq.y, dq.z, dq.w, g + 1) && budget > 0;
             const bool full_next = next_live && window_full(m, (g + 1) * kStepSamples);
-            if (lane == 0) cs_set_q(cs, CS_B, b, g, budget, (next_live ? kNextLive : 0) | (full_next ? kNextFull : 0));
+            if (lane == 0) {
+                cs_set_q(cs, CS_B, b, g, budget, (next_live ? kNextLive : 0) | (full_next ? kNextFull : 0));
+                cs[CS_CARRY] = __float_as_int(carry);
+            }
         }
         __syncwarp();
-        process_group<EXACT, MELSPEC>(p, TAB, WS, lane);
+        process_group<MELSPEC>(p, TAB, WS, lane, ra, rc);
         staged = next_live;
         {  // advance (CS_B / CS_G are read by process_group, so they move only now)
             const int4 l2 = cs_q(cs, CS_B);

@@ -149,14 +149,14 @@ class GpuFbankFrontend:
         _lib.check(self.lib.psla_frontend_set_cost_model(self._h, int(live), int(dead), int(cold)), "set_cost_model", self._h)
 
     def set_trace(self, enable: bool) -> Optional[torch.Tensor]:
-        """Per-warp timeline of the streaming kernel (see psla_frontend_set_trace).  Returns the int64 [warps, 32]
+        """Per-warp timeline of the streaming kernel (see psla_frontend_set_trace).  Returns the int64 [warps, words]
         device tensor the next forward calls fill, or None when switched off."""
         if not enable:
             _lib.check(self.lib.psla_frontend_set_trace(self._h, None, 0), "set_trace", self._h)
             self._trace = None
             return None
         n = int(self.lib.psla_frontend_trace_records(self._h))
-        self._trace = torch.zeros((n // 8, 32), dtype=torch.int64, device=self.device)
+        self._trace = torch.zeros((n, int(self.lib.psla_frontend_trace_words())), dtype=torch.int64, device=self.device)
         _lib.check(self.lib.psla_frontend_set_trace(self._h, self._trace.data_ptr(), n), "set_trace", self._h)
         return self._trace
 

@@ -67,6 +67,7 @@ def main():
     recs = []
     for k in range(8):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        tr.zero_()
         e0.record()
         fe.forward_packed(sets[k % 4], src1, src2, lam, masks, out=outs[k % 4])
         e1.record()
@@ -94,25 +95,36 @@ def main():
         print("live groups     ", pct(live[ok]))
         print("dead groups     ", pct(dead[ok]))
         print("cold starts     ", pct(cold[ok]))
-        # per-step durations by kind and by position in the warp's sequence
-        steps = r[:, 4:]
-        cyc = steps & ((1 << 40) - 1)
-        kind = (steps >> 40) & 0xF
-        ngrp = (steps >> 44) & 0xFFFF
-        nxt = np.concatenate([cyc[:, 1:], np.zeros((len(cyc), 1), dtype=cyc.dtype)], axis=1)
-        valid_next = np.concatenate([kind[:, 1:] > 0, np.zeros((len(cyc), 1), dtype=bool)], axis=1)
-        last = (kind > 0) & ~valid_next
-        dur = np.where(valid_next, nxt - cyc, 0)
-        dur = np.where(last, tot[:, None] - cyc, dur)  # the last step ends with the warp
-        for kk, name in ((1, "live"), (2, "cold+live"), (3, "dead run")):
-            m = (kind == kk) & ok[:, None]
-            if m.any():
-                d = dur[m]
-                print(f"step cycles {name:10s}", pct(d), f"  n={m.sum()}  groups/step {ngrp[m].mean():.1f}")
-        for pos in range(0, 12):
-            m = (kind[:, pos] == 1) & ok
-            if m.any():
-                print(f"  live step at position {pos:2d}: median {np.median(dur[m, pos]):8.0f} cycles  start at {np.median(cyc[m, pos]):8.0f}")
+        # events -> steps with phase markers
+        ev = r[:, 4:]
+        phases = {1: {}, 2: {}, 3: {}}
+        names = {4: "clip entered", 5: "window staged", 6: "pass 1 done", 7: "pass 2 + power done", 8: "mel done", 9: "epilogue done", 10: "cold loads issued", 11: "prefetch issued", 99: "step end"}
+        for wi in np.nonzero(ok)[0]:
+            row = ev[wi]
+            cyc = row & ((1 << 40) - 1)
+            kind = (row >> 40) & 0xF
+            n_ev = int((kind > 0).sum())
+            opens = [i for i in range(n_ev) if kind[i] <= 3]
+            for j, i in enumerate(opens):
+                last_open = j + 1 == len(opens)
+                if last_open and n_ev == len(row):
+                    continue  # record full: the end of this step is unknown
+                end_i = opens[j + 1] if not last_open else n_ev
+                t_end = int(cyc[end_i]) if not last_open else int(tot[wi])
+                prev = int(cyc[i])
+                d = phases[int(kind[i])]
+                for q in range(i + 1, end_i):
+                    d.setdefault(int(kind[q]), []).append(int(cyc[q]) - prev)
+                    prev = int(cyc[q])
+                d.setdefault(99, []).append(t_end - prev)
+                d.setdefault(100, []).append(t_end - int(cyc[i]))
+        for kk, name in ((1, "live step"), (2, "cold-started live step"), (3, "dead run")):
+            d = phases[kk]
+            if not d:
+                continue
+            print(f"{name}: n={len(d[100])}  whole step cycles", pct(np.array(d[100])))
+            for q in [k for k in (4, 10, 5, 6, 7, 11, 8, 9, 99) if k in d]:
+                print(f"    -> {names[q]:22s}", pct(np.array(d[q])), f" n={len(d[q])}")
         sm_end = {}
         for s_, e, lv in zip(smid[ok], t1[ok], live[ok]):
             a_ = sm_end.setdefault(int(s_), [0, 0])

@@ -126,6 +126,11 @@ int psla_frontend_trace_words(void);
  * computed group after constant rows / at a clip start.  Defaults are measured on B200. */
 int psla_frontend_set_cost_model(psla_frontend_t* handle, int live, int dead, int cold);
 
+/* Where the per-call clip descriptors (a few KB) travel to the device: 1 (default) on an internal copy stream, ordered
+ * before the kernel by an event, so that the kernels of consecutive forward() calls run back to back on `stream`;
+ * 0: as a copy on `stream` itself.  Results do not depend on it. */
+int psla_frontend_set_meta_stream(psla_frontend_t* handle, int enable);
+
 const char* psla_strerror(int status);
 int psla_last_cuda_error(const psla_frontend_t* handle);
 const char* psla_version(void);

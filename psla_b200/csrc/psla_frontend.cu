@@ -32,6 +32,8 @@
 // ================================================================================================
 using namespace psla;
 
+constexpr int kMetaSlots = 4;
+
 struct psla_frontend {
     int device = 0;
     int sample_rate = 16000;
@@ -56,14 +58,18 @@ struct psla_frontend {
     std::vector<EvTriple> timed;
     int64_t launches = 0;
     int last_cuda = 0;
-    // pinned descriptor staging ring
+    // Descriptor staging ring: call k fills pinned slot k % kMetaSlots, which is copied to device slot k % kMetaSlots of
+    // the caller's workspace on `copy_stream` (so the copy is off the launch stream: kernels of consecutive calls run
+    // back to back); `copied` orders the kernel after the copy, `done` (recorded after the kernel) guards slot reuse.
     struct Slot {
         void* host = nullptr;
         size_t cap = 0;
-        cudaEvent_t ev = nullptr;
+        cudaEvent_t copied = nullptr, done = nullptr;
         bool pending = false;
-    } slots[4];
+    } slots[kMetaSlots];
     int next_slot = 0;
+    cudaStream_t copy_stream = nullptr;
+    int meta_on_copy_stream = 1;
     // forward_host device buffers
     float* d_wav = nullptr;
     size_t d_wav_cap = 0;
@@ -190,7 +196,10 @@ int psla_frontend_create(psla_frontend_t** handle, int device, int sample_rate, 
     int st = upload_tables(h);
     if (st == PSLA_OK) {
         for (auto& s : h->slots)
-            if (cudaEventCreateWithFlags(&s.ev, cudaEventDisableTiming) != cudaSuccess) st = PSLA_E_CUDA;
+            if (cudaEventCreateWithFlags(&s.copied, cudaEventDisableTiming) != cudaSuccess ||
+                cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming) != cudaSuccess)
+                st = PSLA_E_CUDA;
+        if (cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking) != cudaSuccess) st = PSLA_E_CUDA;
     }
     if (st != PSLA_OK) {
         psla_frontend_destroy(h);
@@ -208,8 +217,10 @@ void psla_frontend_destroy(psla_frontend_t* h) {
         for (auto& e : t.e) cudaEventDestroy(e);
     for (auto& s : h->slots) {
         if (s.host) cudaFreeHost(s.host);
-        if (s.ev) cudaEventDestroy(s.ev);
+        if (s.copied) cudaEventDestroy(s.copied);
+        if (s.done) cudaEventDestroy(s.done);
     }
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->d_tab) cudaFree(h->d_tab);
     if (h->d_wav) cudaFree(h->d_wav);
     if (h->d_out) cudaFree(h->d_out);
@@ -242,9 +253,9 @@ int psla_frontend_get_tables(const psla_frontend_t* h, float* window, float* mel
 
 size_t psla_frontend_workspace_bytes(const psla_frontend_t* h, int n_clips) {
     if (!h || n_clips < 0) return 0;
-    return align_up(static_cast<size_t>(n_clips) * sizeof(ClipDesc), 256) +
-           align_up((static_cast<size_t>(n_clips) + 1) * sizeof(ClipCost), 256) +
-           static_cast<size_t>(n_clips) * kStatSegs * kStatVals * sizeof(double);
+    const size_t meta = align_up(static_cast<size_t>(n_clips) * sizeof(ClipDesc), 256) +
+                        align_up((static_cast<size_t>(n_clips) + 1) * sizeof(ClipCost), 256);
+    return kMetaSlots * meta + static_cast<size_t>(n_clips) * kStatSegs * kStatVals * sizeof(double);
 }
 
 int psla_frontend_num_frames(const psla_frontend_t* h, int64_t n_samples) {
@@ -296,6 +307,12 @@ int psla_frontend_trace_records(const psla_frontend_t* h) {
 
 int psla_frontend_trace_words(void) { return kTraceWords; }
 
+int psla_frontend_set_meta_stream(psla_frontend_t* h, int enable) {
+    if (!h) return PSLA_E_INVALID;
+    h->meta_on_copy_stream = enable ? 1 : 0;
+    return PSLA_OK;
+}
+
 int psla_frontend_set_cost_model(psla_frontend_t* h, int live, int dead, int cold) {
     // total cost of a batch must stay well inside int64 and a warp's budget inside int32
     if (!h || live < 1 || dead < 1 || cold < 0 || live > 4096 || dead > 4096 || cold > 4096) return PSLA_E_INVALID;
@@ -336,12 +353,13 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
     if (!guard.ok) return PSLA_E_CUDA;
 
     // ---- pinned staging slot ----
-    psla_frontend::Slot& slot = h->slots[h->next_slot];
+    const int slot_index = h->next_slot;
+    psla_frontend::Slot& slot = h->slots[slot_index];
     const size_t desc_bytes = align_up(static_cast<size_t>(n_clips) * sizeof(ClipDesc), 256);
     const size_t cost_bytes = align_up((static_cast<size_t>(n_clips) + 1) * sizeof(ClipCost), 256);
     const size_t meta_bytes = desc_bytes + cost_bytes;
     if (slot.pending) {
-        PSLA_CUDA(h, cudaEventSynchronize(slot.ev));
+        PSLA_CUDA(h, cudaEventSynchronize(slot.done));  // the kernel that read this slot (pinned and device copy) is done
         slot.pending = false;
     }
     if (slot.cap < meta_bytes) {
@@ -439,13 +457,18 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
     costs[n_clips].pad2 = 0;
 
     // ---- enqueue ----
-    ClipDesc* d_desc = static_cast<ClipDesc*>(workspace);
-    ClipCost* d_cost = reinterpret_cast<ClipCost*>(static_cast<char*>(workspace) + desc_bytes);
-    double* d_part = reinterpret_cast<double*>(static_cast<char*>(workspace) + meta_bytes);
-    PSLA_CUDA(h, cudaMemcpyAsync(d_desc, descs, meta_bytes, cudaMemcpyHostToDevice, stream));
-    PSLA_CUDA(h, cudaEventRecord(slot.ev, stream));
-    slot.pending = true;
-    h->next_slot = (h->next_slot + 1) % 4;
+    char* d_meta = static_cast<char*>(workspace) + static_cast<size_t>(slot_index) * meta_bytes;
+    ClipDesc* d_desc = reinterpret_cast<ClipDesc*>(d_meta);
+    ClipCost* d_cost = reinterpret_cast<ClipCost*>(d_meta + desc_bytes);
+    double* d_part = reinterpret_cast<double*>(static_cast<char*>(workspace) + kMetaSlots * meta_bytes);
+    if (h->meta_on_copy_stream) {
+        PSLA_CUDA(h, cudaMemcpyAsync(d_meta, descs, meta_bytes, cudaMemcpyHostToDevice, h->copy_stream));
+        PSLA_CUDA(h, cudaEventRecord(slot.copied, h->copy_stream));
+        PSLA_CUDA(h, cudaStreamWaitEvent(stream, slot.copied, 0));
+    } else {
+        PSLA_CUDA(h, cudaMemcpyAsync(d_meta, descs, meta_bytes, cudaMemcpyHostToDevice, stream));
+    }
+    h->next_slot = (h->next_slot + 1) % kMetaSlots;
 
     psla_frontend::EvTriple ev{};
     if (h->timing) {
@@ -501,6 +524,8 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
         else fbank_stream_kernel<false, false><<<grid, kThreads, h->smem_bytes, stream>>>(p);
     }
     PSLA_CUDA(h, cudaGetLastError());
+    PSLA_CUDA(h, cudaEventRecord(slot.done, stream));
+    slot.pending = true;
     if (h->timing) {
         PSLA_CUDA(h, cudaEventRecord(ev.e[2], stream));
         h->timed.push_back(ev);

@@ -148,6 +148,10 @@ class GpuFbankFrontend:
         """Work-partition weights of the streaming kernel (tuning only; see psla_frontend_set_cost_model)."""
         _lib.check(self.lib.psla_frontend_set_cost_model(self._h, int(live), int(dead), int(cold)), "set_cost_model", self._h)
 
+    def set_meta_stream(self, enable: bool):
+        """Descriptor upload on the library's copy stream (default) or on the launch stream (psla_frontend_set_meta_stream)."""
+        _lib.check(self.lib.psla_frontend_set_meta_stream(self._h, int(bool(enable))), "set_meta_stream", self._h)
+
     def set_trace(self, enable: bool) -> Optional[torch.Tensor]:
         """Per-warp timeline of the streaming kernel (see psla_frontend_set_trace).  Returns the int64 [warps, words]
         device tensor the next forward calls fill, or None when switched off."""

@@ -40,6 +40,8 @@ SYMBOLS = {
     "psla_frontend_trace_words": (c_int, []),
     "psla_frontend_set_cost_model": (c_int, [c_void_p, c_int, c_int, c_int]),
     "psla_frontend_set_meta_stream": (c_int, [c_void_p, c_int]),
+    "psla_frontend_set_launch_overlap": (c_int, [c_void_p, c_int]),
+    "psla_frontend_set_param_meta": (c_int, [c_void_p, c_int]),
     "psla_strerror": (c_char_p, [c_int]),
     "psla_last_cuda_error": (c_int, [c_void_p]),
     "psla_version": (c_char_p, []),

@@ -19,6 +19,7 @@
 
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <vector>
@@ -70,6 +71,17 @@ struct psla_frontend {
     int next_slot = 0;
     cudaStream_t copy_stream = nullptr;
     int meta_on_copy_stream = 1;
+    // host-side descriptor build buffers; batches of <= kParamClips clips can be passed as kernel parameters
+    MetaBlock meta_host;
+    std::vector<ClipDesc> big_descs;
+    std::vector<ClipCost> big_costs;
+    int param_meta = 1;
+    // programmatic overlap of consecutive launches (psla_frontend_set_launch_overlap)
+    int pdl = 1;
+    bool prev_valid = false;
+    void* prev_stream = nullptr;
+    const char* prev_out_lo = nullptr;
+    const char* prev_out_hi = nullptr;
     // forward_host device buffers
     float* d_wav = nullptr;
     size_t d_wav_cap = 0;
@@ -106,10 +118,14 @@ size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 template <bool EXACT, bool MELSPEC>
 cudaError_t prepare_kernel(size_t smem) {
-    cudaError_t e = cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(smem));
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    e = cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
 }
 
 int upload_tables(psla_frontend* h) {
@@ -313,6 +329,18 @@ int psla_frontend_set_meta_stream(psla_frontend_t* h, int enable) {
     return PSLA_OK;
 }
 
+int psla_frontend_set_launch_overlap(psla_frontend_t* h, int enable) {
+    if (!h) return PSLA_E_INVALID;
+    h->pdl = enable ? 1 : 0;
+    return PSLA_OK;
+}
+
+int psla_frontend_set_param_meta(psla_frontend_t* h, int enable) {
+    if (!h) return PSLA_E_INVALID;
+    h->param_meta = enable ? 1 : 0;
+    return PSLA_OK;
+}
+
 int psla_frontend_set_cost_model(psla_frontend_t* h, int live, int dead, int cold) {
     // total cost of a batch must stay well inside int64 and a warp's budget inside int32
     if (!h || live < 1 || dead < 1 || cold < 0 || live > 4096 || dead > 4096 || cold > 4096) return PSLA_E_INVALID;
@@ -352,26 +380,17 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
     DeviceGuard guard(h->device);
     if (!guard.ok) return PSLA_E_CUDA;
 
-    // ---- pinned staging slot ----
-    const int slot_index = h->next_slot;
-    psla_frontend::Slot& slot = h->slots[slot_index];
+    // ---- host-side descriptors (plain memory; they travel as kernel parameters or through a pinned slot below) ----
     const size_t desc_bytes = align_up(static_cast<size_t>(n_clips) * sizeof(ClipDesc), 256);
     const size_t cost_bytes = align_up((static_cast<size_t>(n_clips) + 1) * sizeof(ClipCost), 256);
     const size_t meta_bytes = desc_bytes + cost_bytes;
-    if (slot.pending) {
-        PSLA_CUDA(h, cudaEventSynchronize(slot.done));  // the kernel that read this slot (pinned and device copy) is done
-        slot.pending = false;
+    const bool small = n_clips <= kParamClips;
+    if (!small) {
+        if (h->big_descs.size() < static_cast<size_t>(n_clips)) h->big_descs.resize(n_clips);
+        if (h->big_costs.size() < static_cast<size_t>(n_clips) + 1) h->big_costs.resize(static_cast<size_t>(n_clips) + 1);
     }
-    if (slot.cap < meta_bytes) {
-        if (slot.host) cudaFreeHost(slot.host);
-        slot.host = nullptr;
-        slot.cap = 0;
-        const size_t cap = align_up(meta_bytes * 2, 4096);
-        PSLA_CUDA(h, cudaHostAlloc(&slot.host, cap, cudaHostAllocDefault));
-        slot.cap = cap;
-    }
-    ClipDesc* descs = static_cast<ClipDesc*>(slot.host);
-    ClipCost* costs = reinterpret_cast<ClipCost*>(static_cast<char*>(slot.host) + desc_bytes);
+    ClipDesc* descs = small ? h->meta_host.desc : h->big_descs.data();
+    ClipCost* costs = small ? h->meta_host.cost : h->big_costs.data();
     const int G = (target_length + kGroupFrames - 1) / kGroupFrames;
     long long total_cost = 0;
     bool any_stats = false;
@@ -457,18 +476,43 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
     costs[n_clips].pad2 = 0;
 
     // ---- enqueue ----
-    char* d_meta = static_cast<char*>(workspace) + static_cast<size_t>(slot_index) * meta_bytes;
-    ClipDesc* d_desc = reinterpret_cast<ClipDesc*>(d_meta);
-    ClipCost* d_cost = reinterpret_cast<ClipCost*>(d_meta + desc_bytes);
+    // Small batches without a statistics pass read their descriptors from the kernel's parameter space: nothing is
+    // uploaded and nothing sits between two launches on the stream.  Otherwise: pinned slot -> device slot of the
+    // workspace on the copy stream, the kernel ordered after it by an event.
+    const bool param_meta = small && !any_stats && h->param_meta;
+    ClipDesc* d_desc = nullptr;
+    ClipCost* d_cost = nullptr;
     double* d_part = reinterpret_cast<double*>(static_cast<char*>(workspace) + kMetaSlots * meta_bytes);
-    if (h->meta_on_copy_stream) {
-        PSLA_CUDA(h, cudaMemcpyAsync(d_meta, descs, meta_bytes, cudaMemcpyHostToDevice, h->copy_stream));
-        PSLA_CUDA(h, cudaEventRecord(slot.copied, h->copy_stream));
-        PSLA_CUDA(h, cudaStreamWaitEvent(stream, slot.copied, 0));
-    } else {
-        PSLA_CUDA(h, cudaMemcpyAsync(d_meta, descs, meta_bytes, cudaMemcpyHostToDevice, stream));
+    psla_frontend::Slot* slot = nullptr;
+    if (!param_meta) {
+        const int slot_index = h->next_slot;
+        slot = &h->slots[slot_index];
+        if (slot->pending) {
+            PSLA_CUDA(h, cudaEventSynchronize(slot->done));  // the kernel that read this slot (pinned and device copy) is done
+            slot->pending = false;
+        }
+        if (slot->cap < meta_bytes) {
+            if (slot->host) cudaFreeHost(slot->host);
+            slot->host = nullptr;
+            slot->cap = 0;
+            const size_t cap = align_up(meta_bytes * 2, 4096);
+            PSLA_CUDA(h, cudaHostAlloc(&slot->host, cap, cudaHostAllocDefault));
+            slot->cap = cap;
+        }
+        std::memcpy(slot->host, descs, static_cast<size_t>(n_clips) * sizeof(ClipDesc));
+        std::memcpy(static_cast<char*>(slot->host) + desc_bytes, costs, (static_cast<size_t>(n_clips) + 1) * sizeof(ClipCost));
+        char* d_meta = static_cast<char*>(workspace) + static_cast<size_t>(slot_index) * meta_bytes;
+        d_desc = reinterpret_cast<ClipDesc*>(d_meta);
+        d_cost = reinterpret_cast<ClipCost*>(d_meta + desc_bytes);
+        if (h->meta_on_copy_stream) {
+            PSLA_CUDA(h, cudaMemcpyAsync(d_meta, slot->host, meta_bytes, cudaMemcpyHostToDevice, h->copy_stream));
+            PSLA_CUDA(h, cudaEventRecord(slot->copied, h->copy_stream));
+            PSLA_CUDA(h, cudaStreamWaitEvent(stream, slot->copied, 0));
+        } else {
+            PSLA_CUDA(h, cudaMemcpyAsync(d_meta, slot->host, meta_bytes, cudaMemcpyHostToDevice, stream));
+        }
+        h->next_slot = (h->next_slot + 1) % kMetaSlots;
     }
-    h->next_slot = (h->next_slot + 1) % kMetaSlots;
 
     psla_frontend::EvTriple ev{};
     if (h->timing) {
@@ -515,17 +559,45 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
     p.c1 = static_cast<float>(1.0 - static_cast<double>(h->preemph));
     p.cm = h->cm;
     p.trace = h->trace;
-    const dim3 grid(h->num_sms > 0 ? h->num_sms : 148);
-    if (h->exact_mean) {
-        if (h->mel_spec) fbank_stream_kernel<true, true><<<grid, kThreads, h->smem_bytes, stream>>>(p);
-        else fbank_stream_kernel<true, false><<<grid, kThreads, h->smem_bytes, stream>>>(p);
-    } else {
-        if (h->mel_spec) fbank_stream_kernel<false, true><<<grid, kThreads, h->smem_bytes, stream>>>(p);
-        else fbank_stream_kernel<false, false><<<grid, kThreads, h->smem_bytes, stream>>>(p);
+    // Overlap with the previous forward() of this handle (its tail SMs start this launch's CTAs) when nothing can
+    // conflict: same stream, no statistics kernel in between, disjoint output ranges, no tracing.
+    const char* out_lo = reinterpret_cast<const char*>(out);
+    const char* out_hi = out_lo + static_cast<size_t>(n_clips) * target_length * h->nmel * sizeof(float);
+    const bool overlap_ok = h->pdl && param_meta && !h->trace && !h->timing && h->prev_valid && h->prev_stream == stream_ &&
+                            (out_hi <= h->prev_out_lo || out_lo >= h->prev_out_hi);
+    h->prev_valid = true;
+    h->prev_stream = stream_;
+    h->prev_out_lo = out_lo;
+    h->prev_out_hi = out_hi;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(h->num_sms > 0 ? h->num_sms : 148);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = h->smem_bytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = overlap_ok ? 1 : 0;
+    const int variant = (h->exact_mean ? 4 : 0) | (h->mel_spec ? 2 : 0) | (param_meta ? 1 : 0);
+    cudaError_t le = cudaSuccess;
+    const MetaNone none = {0};
+    switch (variant) {
+        case 0: le = cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, false, false>, p, none); break;
+        case 1: le = cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, false, true>, p, h->meta_host); break;
+        case 2: le = cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, true, false>, p, none); break;
+        case 3: le = cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, true, true>, p, h->meta_host); break;
+        case 4: le = cudaLaunchKernelEx(&cfg, fbank_stream_kernel<true, false, false>, p, none); break;
+        case 5: le = cudaLaunchKernelEx(&cfg, fbank_stream_kernel<true, false, true>, p, h->meta_host); break;
+        case 6: le = cudaLaunchKernelEx(&cfg, fbank_stream_kernel<true, true, false>, p, none); break;
+        default: le = cudaLaunchKernelEx(&cfg, fbank_stream_kernel<true, true, true>, p, h->meta_host); break;
     }
+    PSLA_CUDA(h, le);
     PSLA_CUDA(h, cudaGetLastError());
-    PSLA_CUDA(h, cudaEventRecord(slot.done, stream));
-    slot.pending = true;
+    if (slot) {
+        PSLA_CUDA(h, cudaEventRecord(slot->done, stream));
+        slot->pending = true;
+    }
     if (h->timing) {
         PSLA_CUDA(h, cudaEventRecord(ev.e[2], stream));
         h->timed.push_back(ev);

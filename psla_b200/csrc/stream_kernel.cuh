@@ -95,6 +95,33 @@ __device__ __forceinline__ ClipCost load_cost(const ClipCost* __restrict__ p) {
     return u.c;
 }
 
+// Where the kernel reads the clip descriptors and the cost table from: device memory (any batch size; uploaded per call),
+// or, for batches of at most kParamClips clips, the kernel's own parameter space (no upload, nothing between two launches
+// on the stream, which is what lets consecutive launches overlap; see psla_frontend.cu).
+constexpr int kParamClips = 128;
+struct MetaBlock {
+    ClipCost cost[kParamClips + 1];
+    ClipDesc desc[kParamClips];
+};
+struct MetaNone {
+    int unused;
+};
+struct GlobalMeta {
+    const ClipDesc* desc_;
+    const ClipCost* cost_;
+    static constexpr bool kWarpSearch = true;  // lanes may read different entries at full speed
+    __device__ __forceinline__ ClipDesc desc(int b) const { return load_desc(desc_ + b); }
+    __device__ __forceinline__ ClipCost cost(int b) const { return load_cost(cost_ + b); }
+    __device__ __forceinline__ long long cum(int b) const { return __ldg(&cost_[b].cum); }
+};
+struct ParamMeta {
+    const MetaBlock* blk;
+    static constexpr bool kWarpSearch = false;  // constant-bank reads want a warp-uniform index
+    __device__ __forceinline__ ClipDesc desc(int b) const { return blk->desc[b]; }
+    __device__ __forceinline__ ClipCost cost(int b) const { return blk->cost[b]; }
+    __device__ __forceinline__ long long cum(int b) const { return blk->cost[b].cum; }
+};
+
 // 4 consecutive samples [i, i+4) of a waveform of n samples, zeros past the end
 __device__ __forceinline__ float4 load4(const float* __restrict__ w, int i, int n, bool aligned) {
     if (aligned && i + 3 < n) return __ldg(reinterpret_cast<const float4*>(w + i));
@@ -384,26 +411,35 @@ __host__ __device__ __forceinline__ int cost_before(const CostModel& cm, int a_l
 }
 
 // First group (b, g) in clip-major order whose preceding cost is >= target; returns that preceding cost.
-// Warp-cooperative (all lanes return the same): the clip is found by a 128-ary search over the cumulative costs, one
-// round trip to L2 per level instead of one per bit.
-__device__ __forceinline__ long long find_start(const ClipCost* __restrict__ cost, const CostModel& cm, int n_clips, int G, long long target,
-                                                int lane, int& b_out, int& g_out) {
+// Warp-cooperative (all lanes return the same).  From device memory the clip is found by a 128-ary search over the
+// cumulative costs, one round trip to L2 per level instead of one per bit; from parameter space by a plain binary search.
+template <class MS>
+__device__ __forceinline__ long long find_start(const MS& ms, const CostModel& cm, int n_clips, int G, long long target, int lane,
+                                                int& b_out, int& g_out) {
     int lo = 0, hi = n_clips;  // largest b in [lo, hi] with cum[b] <= target (cum[0] == 0)
-    while (lo < hi) {
-        const int step = (hi - lo + 127) >> 7;
-        long long v[4];
+    if (MS::kWarpSearch) {
+        while (lo < hi) {
+            const int step = (hi - lo + 127) >> 7;
+            long long v[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) v[j] = __ldg(&cost[min(hi, lo + (4 * lane + j + 1) * step)].cum);
-        int cnt = 0;  // candidates lo + k*step, k = 1..128 (clipped to hi) are monotone: the first cnt of them pass
+            for (int j = 0; j < 4; ++j) v[j] = ms.cum(min(hi, lo + (4 * lane + j + 1) * step));
+            int cnt = 0;  // candidates lo + k*step, k = 1..128 (clipped to hi) are monotone: the first cnt of them pass
 #pragma unroll
-        for (int j = 0; j < 4; ++j) cnt += __popc(__ballot_sync(0xffffffffu, v[j] <= target));
-        const int nlo = min(hi, lo + cnt * step);
-        if (cnt < 128) hi = min(hi, lo + (cnt + 1) * step) - 1;
-        lo = nlo;
+            for (int j = 0; j < 4; ++j) cnt += __popc(__ballot_sync(0xffffffffu, v[j] <= target));
+            const int nlo = min(hi, lo + cnt * step);
+            if (cnt < 128) hi = min(hi, lo + (cnt + 1) * step) - 1;
+            lo = nlo;
+        }
+    } else {
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (ms.cum(mid) <= target) lo = mid;
+            else hi = mid - 1;
+        }
     }
     b_out = lo;
     g_out = 0;
-    const ClipCost c = load_cost(cost + lo);
+    const ClipCost c = ms.cost(lo);
     if (lo >= n_clips) return c.cum;
     const int rem = static_cast<int>(target - c.cum);
     if (rem <= 0) return c.cum;
@@ -415,7 +451,7 @@ __device__ __forceinline__ long long find_start(const ClipCost* __restrict__ cos
     }
     if (glo >= G) {
         b_out = lo + 1;
-        return __ldg(&cost[lo + 1].cum);
+        return ms.cum(lo + 1);
     }
     g_out = glo;
     return c.cum + cost_before(cm, c.a_lo, c.a_hi, c.b_lo, glo);
@@ -436,10 +472,10 @@ __device__ __forceinline__ void warp_fill(float* __restrict__ ptr, long long cou
 }
 
 // load a clip's descriptor, derive its conditioning constants, park everything in the warp's clip-state words
-template <bool EXACT>
-__device__ __forceinline__ void enter_clip(const StreamParams& p, int b, int lane, int* cs) {
-    const ClipDesc d = load_desc(p.desc + b);
-    const ClipCost cc = load_cost(p.cost + b);
+template <bool EXACT, class MS>
+__device__ __forceinline__ void enter_clip(const StreamParams& p, const MS& ms, int b, int lane, int* cs) {
+    const ClipDesc d = ms.desc(b);
+    const ClipCost cc = ms.cost(b);
     const bool mix = d.n2 > 0;
     const int nmin = min(d.n1, d.n2);
     float sub1 = 0.f, mean2 = 0.f, mixmean = 0.f;
@@ -691,13 +727,24 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
 // Kernel 2: the streaming kernel.  grid = one CTA per SM, block = 16 warps, no CTA barrier after the table load.
 // Warp r of W owns the groups whose preceding cost lies in [r*C/W, (r+1)*C/W)  (clip-major order).
 // ------------------------------------------------------------------------------------------------
-template <bool EXACT, bool MELSPEC>
-__global__ void __launch_bounds__(kThreads, 1) fbank_stream_kernel(const StreamParams p) {
+template <bool EXACT, bool MELSPEC, bool PMETA>
+__global__ void __launch_bounds__(kThreads, 1)
+    fbank_stream_kernel(const __grid_constant__ StreamParams p, const __grid_constant__ std::conditional_t<PMETA, MetaBlock, MetaNone> meta) {
+    using MS = std::conditional_t<PMETA, ParamMeta, GlobalMeta>;
+    MS ms;
+    if constexpr (PMETA) ms.blk = &meta;
+    else {
+        ms.desc_ = p.desc;
+        ms.cost_ = p.cost;
+    }
     extern __shared__ __align__(16) float smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     float* TAB = smem;
     float* WS = smem + p.tab_floats + warp * kWarpFloats;
     int* cs = reinterpret_cast<int*>(WS + kWsCS);
+    // The next launch on the stream may begin as soon as SMs free up (only effective when the host launched it with
+    // programmatic stream serialization, which it does only when that launch cannot conflict with this one).
+    asm volatile("griddepcontrol.launch_dependents;");
     // ---- prologue: the table copy and the partition search overlap (both are round trips to L2) ----
     const int n4 = p.tab_floats / 4;
     const float4* tsrc = reinterpret_cast<const float4*>(p.tab);
@@ -711,7 +758,7 @@ __global__ void __launch_bounds__(kThreads, 1) fbank_stream_kernel(const StreamP
     const bool has_work = c_lo < c_hi;
     if (has_work) {
         int b, g;
-        const long long start_cost = find_start(p.cost, p.cm, p.n_clips, p.G, c_lo, lane, b, g);
+        const long long start_cost = find_start(ms, p.cm, p.n_clips, p.G, c_lo, lane, b, g);
         // groups are taken while the cost consumed is < budget
         if (lane == 0) cs_set_q(cs, CS_B, b, g, static_cast<int>(c_hi - start_cost), 0);
     }
@@ -736,7 +783,7 @@ __global__ void __launch_bounds__(kThreads, 1) fbank_stream_kernel(const StreamP
         int budget = ls.z;
         if (b >= p.n_clips || budget <= 0) break;
         if (b != loaded_b) {
-            enter_clip<EXACT>(p, b, lane, cs);
+            enter_clip<EXACT>(p, ms, b, lane, cs);
             loaded_b = b;
             staged = false;
             if (p.trace) trace_phase(p, cs, lane, 4);

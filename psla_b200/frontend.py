@@ -152,6 +152,14 @@ class GpuFbankFrontend:
         """Descriptor upload on the library's copy stream (default) or on the launch stream (psla_frontend_set_meta_stream)."""
         _lib.check(self.lib.psla_frontend_set_meta_stream(self._h, int(bool(enable))), "set_meta_stream", self._h)
 
+    def set_launch_overlap(self, enable: bool):
+        """Programmatic overlap of consecutive launches (psla_frontend_set_launch_overlap)."""
+        _lib.check(self.lib.psla_frontend_set_launch_overlap(self._h, int(bool(enable))), "set_launch_overlap", self._h)
+
+    def set_param_meta(self, enable: bool):
+        """Clip descriptors of small batches as kernel parameters (default) or uploaded (psla_frontend_set_param_meta)."""
+        _lib.check(self.lib.psla_frontend_set_param_meta(self._h, int(bool(enable))), "set_param_meta", self._h)
+
     def set_trace(self, enable: bool) -> Optional[torch.Tensor]:
         """Per-warp timeline of the streaming kernel (see psla_frontend_set_trace).  Returns the int64 [warps, words]
         device tensor the next forward calls fill, or None when switched off."""

@@ -65,6 +65,35 @@ def main():
         t1 = time.perf_counter()
         torch.cuda.synchronize()
         print(f"descriptor copy on the copy stream: {on}: {us:.2f} us/step; host time per call {(t1 - t0) / 200 * 1e6:.1f} us")
+    for on in (True, False, True):
+        fe.set_param_meta(on)
+        us = time_steps()
+        print(f"descriptors as kernel parameters: {on}: {us:.2f} us/step")
+    for on in (True, False, True):
+        fe.set_launch_overlap(on)
+        us = time_steps()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for k in range(3):
+            fe.forward_packed(sets[k % 4], src1, src2, lam, masks, out=outs[k % 4])
+        t1 = time.perf_counter()
+        torch.cuda.synchronize()
+        print(f"launch overlap: {on}: {us:.2f} us/step; host time per call (3 calls, queue empty) {(t1 - t0) / 3 * 1e6:.1f} us")
+    # overlapped launches must give the same results as plain ones
+    fe.set_launch_overlap(False)
+    plain = []
+    for k in range(4):
+        fe.forward_packed(sets[k], src1, src2, lam, masks, out=outs[k])
+    torch.cuda.synchronize()
+    plain = [o.clone() for o in outs]
+    fe.set_launch_overlap(True)
+    for rep in range(5):
+        for k in range(4):
+            outs[k].zero_()
+        for k in range(4):
+            fe.forward_packed(sets[k], src1, src2, lam, masks, out=outs[k])
+        torch.cuda.synchronize()
+        print("overlapped launches identical to plain:", all(bool(torch.equal(a, c)) for a, c in zip(plain, outs)))
     ref = outs[0].clone()
     for cm in [(64, 2, 48), (64, 2, 0), (64, 4, 48), (64, 1, 48), (64, 2, 32), (64, 2, 64), (64, 8, 48), (32, 1, 0)]:
         fe.set_cost_model(*cm)

@@ -222,6 +222,54 @@ def test_deterministic_and_batch_independent(fe):
     assert torch.equal(c[0], a[2])
 
 
+def test_launch_plumbing_does_not_change_results(fe):
+    """Descriptors as kernel parameters vs uploaded, launch overlap, copy stream, cost model: identical bits.  A batch
+    above the 128-clip parameter-space limit (upload path) equals the same clips computed in small batches."""
+    from psla_b200 import params as P
+    from psla_b200.frontend import pack_waveforms
+    torch.manual_seed(5)
+    waves = [synth_wave(300 + i, 16000 + 977 * i) for i in range(12)]
+    packed = pack_waveforms(waves, device=fe.device)
+    B = 150
+    src1 = np.arange(B, dtype=np.int32) % 12
+    src2 = np.where(np.arange(B) % 3 == 0, (np.arange(B) + 5) % 12, -1).astype(np.int32)
+    lam = np.random.default_rng(3).beta(10, 10, B)
+    masks = np.array([P.draw_masks(48, 60, 128, 200) for _ in range(B)], dtype=np.int32)
+    big = fe.forward_packed(packed, src1, src2, lam, masks, target_length=200).cpu()
+    parts = [fe.forward_packed(packed, src1[i:i + 50], src2[i:i + 50], lam[i:i + 50], masks[i:i + 50], target_length=200).cpu()
+             for i in range(0, B, 50)]
+    assert torch.equal(big, torch.cat(parts))
+    # clips whose partner is longer need no statistics pass (fused-mean mode): these go through parameter space
+    n = 50
+    s1 = (np.arange(n) % 6).astype(np.int32)
+    s2 = np.where(np.arange(n) % 3 == 0, 6 + np.arange(n) % 6, -1).astype(np.int32)
+    args = (packed, s1, s2, lam[:n], masks[:n])
+    ref = fe.forward_packed(*args, target_length=200).cpu()
+    try:
+        for setter, val in ((fe.set_param_meta, False), (fe.set_launch_overlap, False), (fe.set_meta_stream, False)):
+            setter(val)
+            outs = [torch.empty(n, 200, 128, device=fe.device) for _ in range(3)]
+            for o in outs:  # back-to-back launches into different buffers (what the overlap path keys on)
+                fe.forward_packed(*args, out=o, target_length=200)
+            torch.cuda.synchronize()
+            assert all(torch.equal(o.cpu(), ref) for o in outs)
+            setter(True)
+        outs = [torch.empty(n, 200, 128, device=fe.device) for _ in range(4)]
+        for rep in range(3):
+            for o in outs:
+                fe.forward_packed(*args, out=o, target_length=200)
+            fe.forward_packed(*args, out=outs[3], target_length=200)  # same buffer twice in a row: no overlap allowed
+        torch.cuda.synchronize()
+        assert all(torch.equal(o.cpu(), ref) for o in outs)
+        fe.set_cost_model(32, 1, 0)
+        assert torch.equal(fe.forward_packed(*args, target_length=200).cpu(), ref)
+    finally:
+        fe.set_param_meta(True)
+        fe.set_launch_overlap(True)
+        fe.set_meta_stream(True)
+        fe.set_cost_model(64, 2, 48)
+
+
 def test_c2_audioset_train_batch(fe):
     """C2: 100 clips, 150 waveforms, every even clip mixed, masks drawn like the reference (48 / 192)."""
     B = 100

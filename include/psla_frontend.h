@@ -87,6 +87,19 @@ int psla_frontend_forward_host(psla_frontend_t* handle, const float* wav_host, c
                                float* out_host, void* stream);
 float* psla_frontend_device_out(const psla_frontend_t* handle);
 
+/* The same two calls for 16-bit PCM waveforms as they come out of a wav file (the reference decodes them with
+ * torchaudio.load, audioset_dataset.py:91,95-96, whose normalisation is value / 32768; the kernel applies exactly that
+ * scale, so the features equal those of the fp32 entry points fed with the decoded floats bit for bit).  Half the input
+ * bytes over PCIe and HBM.  Offsets and lengths are in samples; `wav` 16-byte aligned. */
+int psla_frontend_forward_pcm16(psla_frontend_t* handle, const int16_t* wav, const int64_t* wav_offset, const int64_t* wav_length,
+                                int n_wav, const int32_t* src1, const int32_t* src2, const double* lambda, const int32_t* mask,
+                                int n_clips, int target_length, float norm_mean, float norm_div, int skip_norm,
+                                float* out, void* workspace, size_t workspace_bytes, void* stream);
+int psla_frontend_forward_host_pcm16(psla_frontend_t* handle, const int16_t* wav_host, const int64_t* wav_offset,
+                                     const int64_t* wav_length, int n_wav, const int32_t* src1, const int32_t* src2,
+                                     const double* lambda, const int32_t* mask, int n_clips, int target_length, float norm_mean,
+                                     float norm_div, int skip_norm, float* out_host, void* stream);
+
 /* Number of frames kaldi.fbank produces for n_samples (snip_edges=True, kaldi.py:63-67); < 0 if too short. */
 int psla_frontend_num_frames(const psla_frontend_t* handle, int64_t n_samples);
 /* Kernels launched by this handle since creation (bench.py reports it as gpu_launches). */

@@ -29,6 +29,12 @@ SYMBOLS = {
                                            POINTER(c_double), POINTER(c_int32), c_int, c_int, c_float, c_float, c_int,
                                            c_void_p, c_void_p]),
     "psla_frontend_device_out": (c_void_p, [c_void_p]),
+    "psla_frontend_forward_pcm16": (c_int, [c_void_p, c_void_p, POINTER(c_int64), POINTER(c_int64), c_int, POINTER(c_int32), POINTER(c_int32),
+                                            POINTER(c_double), POINTER(c_int32), c_int, c_int, c_float, c_float, c_int,
+                                            c_void_p, c_void_p, c_size_t, c_void_p]),
+    "psla_frontend_forward_host_pcm16": (c_int, [c_void_p, c_void_p, POINTER(c_int64), POINTER(c_int64), c_int, POINTER(c_int32),
+                                                 POINTER(c_int32), POINTER(c_double), POINTER(c_int32), c_int, c_int, c_float, c_float,
+                                                 c_int, c_void_p, c_void_p]),
     "psla_frontend_num_frames": (c_int, [c_void_p, c_int64]),
     "psla_frontend_launch_count": (c_int64, [c_void_p]),
     "psla_frontend_set_fast_log": (c_int, [c_void_p, c_int]),

@@ -116,16 +116,36 @@ struct DeviceGuard {
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-template <bool EXACT, bool MELSPEC>
-cudaError_t prepare_kernel(size_t smem) {
-    cudaError_t e = cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+template <bool EXACT, bool MELSPEC, bool PMETA, class S>
+cudaError_t prepare_one(size_t smem) {
+    cudaError_t e = cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC, PMETA, S>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(smem));
     if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-    if (e != cudaSuccess) return e;
-    e = cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC, false>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-    if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC, true>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    return cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC, PMETA, S>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+}
+template <bool EXACT, bool MELSPEC>
+cudaError_t prepare_kernel(size_t smem) {
+    cudaError_t e = prepare_one<EXACT, MELSPEC, false, float>(smem);
+    if (e == cudaSuccess) e = prepare_one<EXACT, MELSPEC, true, float>(smem);
+    if (e == cudaSuccess) e = prepare_one<EXACT, MELSPEC, false, short>(smem);
+    if (e == cudaSuccess) e = prepare_one<EXACT, MELSPEC, true, short>(smem);
+    return e;
+}
+
+// launch of the variant selected at run time
+template <class S>
+cudaError_t launch_stream_kernel(const cudaLaunchConfig_t& cfg, bool exact, bool spec, bool pmeta, const StreamParams& p, const MetaBlock& mb) {
+    const MetaNone none = {0};
+    switch ((exact ? 4 : 0) | (spec ? 2 : 0) | (pmeta ? 1 : 0)) {
+        case 0: return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, false, false, S>, p, none);
+        case 1: return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, false, true, S>, p, mb);
+        case 2: return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, true, false, S>, p, none);
+        case 3: return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, true, true, S>, p, mb);
+        case 4: return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<true, false, false, S>, p, none);
+        case 5: return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<true, false, true, S>, p, mb);
+        case 6: return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<true, true, false, S>, p, none);
+        default: return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<true, true, true, S>, p, mb);
+    }
 }
 
 int upload_tables(psla_frontend* h) {
@@ -362,11 +382,12 @@ int psla_frontend_set_exact_clip_mean(psla_frontend_t* h, int enable) {
     return PSLA_OK;
 }
 
-int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* wav_offset, const int64_t* wav_length,
-                          int n_wav, const int32_t* src1,
-                          const int32_t* src2, const double* lambda, const int32_t* mask, int n_clips, int target_length,
-                          float norm_mean, float norm_div, int skip_norm, float* out, void* workspace,
-                          size_t workspace_bytes, void* stream_) {
+}  // extern "C"
+
+namespace {
+int forward_any(psla_frontend_t* h, const void* wav, bool pcm16, const int64_t* wav_offset, const int64_t* wav_length, int n_wav,
+                const int32_t* src1, const int32_t* src2, const double* lambda, const int32_t* mask, int n_clips, int target_length,
+                float norm_mean, float norm_div, int skip_norm, float* out, void* workspace, size_t workspace_bytes, void* stream_) {
     if (!h || !wav_offset || !wav_length || !src1 || n_wav < 0 || n_clips < 0 || target_length < 1) return PSLA_E_INVALID;
     if (n_clips == 0) return PSLA_OK;
     if (!wav || !out) return PSLA_E_INVALID;
@@ -520,7 +541,8 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
         PSLA_CUDA(h, cudaEventRecord(ev.e[0], stream));
     }
     if (any_stats) {
-        clip_stats_kernel<<<dim3(kStatSegs, n_clips), 256, 0, stream>>>(wav, d_desc, d_part);
+        if (pcm16) clip_stats_kernel<short><<<dim3(kStatSegs, n_clips), 256, 0, stream>>>(static_cast<const short*>(wav), d_desc, d_part);
+        else clip_stats_kernel<float><<<dim3(kStatSegs, n_clips), 256, 0, stream>>>(static_cast<const float*>(wav), d_desc, d_part);
         PSLA_CUDA(h, cudaGetLastError());
         h->launches += 1;
     }
@@ -579,19 +601,8 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = overlap_ok ? 1 : 0;
-    const int variant = (h->exact_mean ? 4 : 0) | (h->mel_spec ? 2 : 0) | (param_meta ? 1 : 0);
-    cudaError_t le = cudaSuccess;
-    const MetaNone none = {0};
-    switch (variant) {
-        case 0: le = cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, false, false>, p, none); break;
-        case 1: le = cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, false, true>, p, h->meta_host); break;
-        case 2: le = cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, true, false>, p, none); break;
-        case 3: le = cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, true, true>, p, h->meta_host); break;
-        case 4: le = cudaLaunchKernelEx(&cfg, fbank_stream_kernel<true, false, false>, p, none); break;
-        case 5: le = cudaLaunchKernelEx(&cfg, fbank_stream_kernel<true, false, true>, p, h->meta_host); break;
-        case 6: le = cudaLaunchKernelEx(&cfg, fbank_stream_kernel<true, true, false>, p, none); break;
-        default: le = cudaLaunchKernelEx(&cfg, fbank_stream_kernel<true, true, true>, p, h->meta_host); break;
-    }
+    const cudaError_t le = pcm16 ? launch_stream_kernel<short>(cfg, h->exact_mean, h->mel_spec, param_meta, p, h->meta_host)
+                                 : launch_stream_kernel<float>(cfg, h->exact_mean, h->mel_spec, param_meta, p, h->meta_host);
     PSLA_CUDA(h, le);
     PSLA_CUDA(h, cudaGetLastError());
     if (slot) {
@@ -606,13 +617,9 @@ int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* w
     return PSLA_OK;
 }
 
-float* psla_frontend_device_out(const psla_frontend_t* h) { return h ? h->d_out : nullptr; }
-
-int psla_frontend_forward_host(psla_frontend_t* h, const float* wav_host, const int64_t* wav_offset,
-                               const int64_t* wav_length, int n_wav,
-                               const int32_t* src1, const int32_t* src2, const double* lambda, const int32_t* mask,
-                               int n_clips, int target_length, float norm_mean, float norm_div, int skip_norm,
-                               float* out_host, void* stream_) {
+int forward_host_any(psla_frontend_t* h, const void* wav_host, bool pcm16, const int64_t* wav_offset, const int64_t* wav_length, int n_wav,
+                     const int32_t* src1, const int32_t* src2, const double* lambda, const int32_t* mask, int n_clips, int target_length,
+                     float norm_mean, float norm_div, int skip_norm, float* out_host, void* stream_) {
     if (!h || !wav_host || !wav_offset || !wav_length || n_wav < 1 || n_clips < 0 || target_length < 1) return PSLA_E_INVALID;
     if (n_clips == 0) return PSLA_OK;
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
@@ -624,7 +631,7 @@ int psla_frontend_forward_host(psla_frontend_t* h, const float* wav_host, const 
         if (wav_offset[i] + wav_length[i] > total) total = wav_offset[i] + wav_length[i];
     }
     if (total < 1) return PSLA_E_INVALID;
-    const size_t wav_bytes = static_cast<size_t>(total) * sizeof(float);
+    const size_t wav_bytes = static_cast<size_t>(total) * (pcm16 ? sizeof(int16_t) : sizeof(float));
     const size_t out_bytes = static_cast<size_t>(n_clips) * target_length * h->nmel * sizeof(float);
     const size_t ws_bytes = psla_frontend_workspace_bytes(h, n_clips);
     auto grow = [&](void** ptr, size_t* cap, size_t need) -> int {
@@ -646,11 +653,47 @@ int psla_frontend_forward_host(psla_frontend_t* h, const float* wav_host, const 
     if ((st = grow(reinterpret_cast<void**>(&h->d_out), &h->d_out_cap, out_bytes)) != PSLA_OK) return st;
     if ((st = grow(&h->d_ws, &h->d_ws_cap, ws_bytes)) != PSLA_OK) return st;
     PSLA_CUDA(h, cudaMemcpyAsync(h->d_wav, wav_host, wav_bytes, cudaMemcpyHostToDevice, stream));
-    st = psla_frontend_forward(h, h->d_wav, wav_offset, wav_length, n_wav, src1, src2, lambda, mask, n_clips, target_length, norm_mean,
-                               norm_div, skip_norm, h->d_out, h->d_ws, h->d_ws_cap, stream_);
+    st = forward_any(h, h->d_wav, pcm16, wav_offset, wav_length, n_wav, src1, src2, lambda, mask, n_clips, target_length, norm_mean, norm_div,
+                     skip_norm, h->d_out, h->d_ws, h->d_ws_cap, stream_);
     if (st != PSLA_OK) return st;
     if (out_host) PSLA_CUDA(h, cudaMemcpyAsync(out_host, h->d_out, out_bytes, cudaMemcpyDeviceToHost, stream));
     return PSLA_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* wav_offset, const int64_t* wav_length, int n_wav,
+                          const int32_t* src1, const int32_t* src2, const double* lambda, const int32_t* mask, int n_clips,
+                          int target_length, float norm_mean, float norm_div, int skip_norm, float* out, void* workspace,
+                          size_t workspace_bytes, void* stream) {
+    return forward_any(h, wav, false, wav_offset, wav_length, n_wav, src1, src2, lambda, mask, n_clips, target_length, norm_mean, norm_div,
+                       skip_norm, out, workspace, workspace_bytes, stream);
+}
+
+int psla_frontend_forward_pcm16(psla_frontend_t* h, const int16_t* wav, const int64_t* wav_offset, const int64_t* wav_length, int n_wav,
+                                const int32_t* src1, const int32_t* src2, const double* lambda, const int32_t* mask, int n_clips,
+                                int target_length, float norm_mean, float norm_div, int skip_norm, float* out, void* workspace,
+                                size_t workspace_bytes, void* stream) {
+    return forward_any(h, wav, true, wav_offset, wav_length, n_wav, src1, src2, lambda, mask, n_clips, target_length, norm_mean, norm_div,
+                       skip_norm, out, workspace, workspace_bytes, stream);
+}
+
+float* psla_frontend_device_out(const psla_frontend_t* h) { return h ? h->d_out : nullptr; }
+
+int psla_frontend_forward_host(psla_frontend_t* h, const float* wav_host, const int64_t* wav_offset, const int64_t* wav_length, int n_wav,
+                               const int32_t* src1, const int32_t* src2, const double* lambda, const int32_t* mask, int n_clips,
+                               int target_length, float norm_mean, float norm_div, int skip_norm, float* out_host, void* stream) {
+    return forward_host_any(h, wav_host, false, wav_offset, wav_length, n_wav, src1, src2, lambda, mask, n_clips, target_length, norm_mean,
+                            norm_div, skip_norm, out_host, stream);
+}
+
+int psla_frontend_forward_host_pcm16(psla_frontend_t* h, const int16_t* wav_host, const int64_t* wav_offset, const int64_t* wav_length,
+                                     int n_wav, const int32_t* src1, const int32_t* src2, const double* lambda, const int32_t* mask,
+                                     int n_clips, int target_length, float norm_mean, float norm_div, int skip_norm, float* out_host,
+                                     void* stream) {
+    return forward_host_any(h, wav_host, true, wav_offset, wav_length, n_wav, src1, src2, lambda, mask, n_clips, target_length, norm_mean,
+                            norm_div, skip_norm, out_host, stream);
 }
 
 }  // extern "C"

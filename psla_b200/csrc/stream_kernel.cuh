@@ -46,7 +46,7 @@ constexpr int kWarpsPerCta = 16;
 constexpr int kThreads = kWarpsPerCta * 32;
 
 struct StreamParams {
-    const float* wav;
+    const void* wav;  // fp32 samples, or int16 PCM (value / 32768, what a decoder's float conversion yields) -- see Pcm<S>
     const ClipDesc* desc;
     const ClipCost* cost;
     const double* partials;
@@ -122,27 +122,64 @@ struct ParamMeta {
     __device__ __forceinline__ long long cum(int b) const { return blk->cost[b].cum; }
 };
 
+// Sample formats.  Pcm<S>::reg_t holds 4 consecutive samples as loaded (fp32: 16 bytes, int16: 8 bytes); the conversion to
+// fp32 happens when the samples are consumed, so that a prefetch is nothing but loads.  int16 PCM converts as
+// value * 2^-15, exactly what a decoder's float conversion yields (torchaudio.load normalises int16 by 32768).
+template <class S>
+struct Pcm;
+template <>
+struct Pcm<float> {
+    using reg_t = float4;
+    static __device__ __forceinline__ reg_t zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
+    static __device__ __forceinline__ reg_t load_vec(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+    static __device__ __forceinline__ float load1(const float* p) { return __ldg(p); }
+    static __device__ __forceinline__ reg_t pack(float x, float y, float z, float w) { return make_float4(x, y, z, w); }
+    static __device__ __forceinline__ float4 to_float4(const reg_t& r) { return r; }
+};
+template <>
+struct Pcm<short> {
+    using reg_t = uint2;
+    static constexpr float kScale = 1.0f / 32768.0f;
+    static __device__ __forceinline__ reg_t zero() { return make_uint2(0u, 0u); }
+    static __device__ __forceinline__ reg_t load_vec(const short* p) { return __ldg(reinterpret_cast<const uint2*>(p)); }
+    static __device__ __forceinline__ float load1(const short* p) { return static_cast<float>(__ldg(p)) * kScale; }
+    static __device__ __forceinline__ reg_t pack(float x, float y, float z, float w) {  // values are exact int16 / 32768
+        const unsigned a = static_cast<unsigned short>(static_cast<short>(x * 32768.0f)), b = static_cast<unsigned short>(static_cast<short>(y * 32768.0f));
+        const unsigned c = static_cast<unsigned short>(static_cast<short>(z * 32768.0f)), d = static_cast<unsigned short>(static_cast<short>(w * 32768.0f));
+        return make_uint2(a | (b << 16), c | (d << 16));
+    }
+    static __device__ __forceinline__ float4 to_float4(const reg_t& r) {
+        float4 v;
+        v.x = static_cast<float>(static_cast<short>(r.x & 0xffffu)) * kScale;
+        v.y = static_cast<float>(static_cast<int>(r.x) >> 16) * kScale;
+        v.z = static_cast<float>(static_cast<short>(r.y & 0xffffu)) * kScale;
+        v.w = static_cast<float>(static_cast<int>(r.y) >> 16) * kScale;
+        return v;
+    }
+};
+
 // 4 consecutive samples [i, i+4) of a waveform of n samples, zeros past the end
-__device__ __forceinline__ float4 load4(const float* __restrict__ w, int i, int n, bool aligned) {
-    if (aligned && i + 3 < n) return __ldg(reinterpret_cast<const float4*>(w + i));
-    float4 v;
-    v.x = (i < n) ? __ldg(w + i) : 0.f;
-    v.y = (i + 1 < n) ? __ldg(w + i + 1) : 0.f;
-    v.z = (i + 2 < n) ? __ldg(w + i + 2) : 0.f;
-    v.w = (i + 3 < n) ? __ldg(w + i + 3) : 0.f;
-    return v;
+template <class S>
+__device__ __forceinline__ typename Pcm<S>::reg_t load4(const S* __restrict__ w, int i, int n, bool aligned) {
+    if (aligned && i + 3 < n) return Pcm<S>::load_vec(w + i);
+    const float x = (i < n) ? Pcm<S>::load1(w + i) : 0.f;
+    const float y = (i + 1 < n) ? Pcm<S>::load1(w + i + 1) : 0.f;
+    const float z = (i + 2 < n) ? Pcm<S>::load1(w + i + 2) : 0.f;
+    const float v = (i + 3 < n) ? Pcm<S>::load1(w + i + 3) : 0.f;
+    return Pcm<S>::pack(x, y, z, v);
 }
 
-// sum of w[lo, hi) by one 256-thread CTA's thread `tid` (strided float4s, 4 loads in flight)
-__device__ __forceinline__ float strided_sum(const float* __restrict__ w, int lo, int hi, int tid, bool aligned) {
+// sum of w[lo, hi) by one 256-thread CTA's thread `tid` (strided groups of 4 samples, 4 loads in flight)
+template <class S>
+__device__ __forceinline__ float strided_sum(const S* __restrict__ w, int lo, int hi, int tid, bool aligned) {
     float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
     int i = lo + 4 * tid;
     if (aligned) {
         for (; i + 3 * 1024 + 3 < hi; i += 4 * 1024) {
-            const float4 a = __ldg(reinterpret_cast<const float4*>(w + i));
-            const float4 b = __ldg(reinterpret_cast<const float4*>(w + i + 1024));
-            const float4 c = __ldg(reinterpret_cast<const float4*>(w + i + 2048));
-            const float4 d = __ldg(reinterpret_cast<const float4*>(w + i + 3072));
+            const float4 a = Pcm<S>::to_float4(Pcm<S>::load_vec(w + i));
+            const float4 b = Pcm<S>::to_float4(Pcm<S>::load_vec(w + i + 1024));
+            const float4 c = Pcm<S>::to_float4(Pcm<S>::load_vec(w + i + 2048));
+            const float4 d = Pcm<S>::to_float4(Pcm<S>::load_vec(w + i + 3072));
             s0 += (a.x + a.y) + (a.z + a.w);
             s1 += (b.x + b.y) + (b.z + b.w);
             s2 += (c.x + c.y) + (c.z + c.w);
@@ -150,7 +187,7 @@ __device__ __forceinline__ float strided_sum(const float* __restrict__ w, int lo
         }
     }
     for (; i < hi; i += 1024) {
-        const float4 v = load4(w, i, hi, aligned);
+        const float4 v = Pcm<S>::to_float4(load4<S>(w, i, hi, aligned));
         s0 += (v.x + v.y) + (v.z + v.w);
     }
     return (s0 + s1) + (s2 + s3);
@@ -161,7 +198,8 @@ __device__ __forceinline__ float strided_sum(const float* __restrict__ w, int lo
 // audioset_dataset.py:92 / :98-99 / :117.  grid = (kStatSegs, B), block = 256.  Deterministic: fixed partition, fixed
 // reduction tree; the streaming kernel adds the kStatSegs partials in a fixed order.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) clip_stats_kernel(const float* __restrict__ wav, const ClipDesc* __restrict__ desc,
+template <class S>
+__global__ void __launch_bounds__(256) clip_stats_kernel(const S* __restrict__ wav, const ClipDesc* __restrict__ desc,
                                                          double* __restrict__ partials) {
     const int b = blockIdx.y, g = blockIdx.x, tid = threadIdx.x;
     const ClipDesc d = load_desc(desc + b);
@@ -255,9 +293,10 @@ __device__ __forceinline__ void cs_set_q(int* cs, int w, int a, int b, int c, in
 //           c is replaced by mean2 (clip statistics are computed for those clips only).
 // FULL: the staged range lies inside both waveforms and both are 16-byte aligned -- no bounds checks, no selects.
 // ------------------------------------------------------------------------------------------------
+template <class S>
 struct MixState {
-    const float* w1;
-    const float* w2;
+    const S* w1;
+    const S* w2;
     float l1, l2;
     float sub1;     // EXACT: mean1;  fused: K = l1*a[0] (+ l2*c[0])
     float mean2;    // EXACT: mean2;  fused: mean2 where the partner is shorter (tail fill)
@@ -266,8 +305,10 @@ struct MixState {
     bool mix, al1, al2;
 };
 
-__device__ __forceinline__ MixState load_mix(const int* cs, const float* wav) {
-    MixState m;
+template <class S>
+__device__ __forceinline__ MixState<S> load_mix(const int* cs, const void* wav_) {
+    const S* wav = static_cast<const S*>(wav_);
+    MixState<S> m;
     const int4 q0 = cs_q(cs, CS_N1), q1 = cs_q(cs, CS_SUB1), q2 = cs_q(cs, CS_OFF1);
     const int fl = q1.w;
     m.w1 = wav + ((static_cast<long long>(q2.y) << 32) | static_cast<unsigned>(q2.x));
@@ -286,12 +327,13 @@ __device__ __forceinline__ MixState load_mix(const int* cs, const float* wav) {
 }
 
 // the group window [S0, S0 + 880) can be staged without bounds checks
-__device__ __forceinline__ bool window_full(const MixState& m, int S0) {
+template <class S>
+__device__ __forceinline__ bool window_full(const MixState<S>& m, int S0) {
     return m.al1 && S0 + kGroupSamples <= m.n1 && (!m.mix || (m.al2 && S0 + kGroupSamples <= m.nmin));
 }
 
-template <bool EXACT, bool FULL>
-__device__ __forceinline__ float mix_sample(const MixState& m, float a, float c, int s) {
+template <bool EXACT, bool FULL, class S>
+__device__ __forceinline__ float mix_sample(const MixState<S>& m, float a, float c, int s) {
     if (!FULL && s >= m.n1) return 0.f;
     if (!m.mix) return __fsub_rn(a, m.sub1);
     if (EXACT) {
@@ -319,32 +361,33 @@ struct StageGeom {
     static constexpr int kLastLane = (kFloat4 - 1) % 32;  // lane holding the range's last float4
 };
 
-template <int U0, int U1, bool FULL, int NIT>
-__device__ __forceinline__ void stage_issue(const MixState& m, int S0, int lane, float4 (&a)[NIT], float4 (&c)[NIT]) {
+template <int U0, int U1, bool FULL, class S, int NIT>
+__device__ __forceinline__ void stage_issue(const MixState<S>& m, int S0, int lane, typename Pcm<S>::reg_t (&a)[NIT],
+                                            typename Pcm<S>::reg_t (&c)[NIT]) {
     using Geo = StageGeom<U0, U1>;
     static_assert(NIT >= Geo::kIters, "register arrays too small");
 #pragma unroll
     for (int it = 0; it < Geo::kIters; ++it) {
         const int L = lane + 32 * it;
         const int s = S0 + U0 + 4 * L;
-        a[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+        a[it] = Pcm<S>::zero();
         c[it] = a[it];
         if ((it + 1) * 32 <= Geo::kFloat4 || L < Geo::kFloat4) {
             if (FULL) {
-                a[it] = __ldg(reinterpret_cast<const float4*>(m.w1 + s));
-                if (m.mix) c[it] = __ldg(reinterpret_cast<const float4*>(m.w2 + s));
+                a[it] = Pcm<S>::load_vec(m.w1 + s);
+                if (m.mix) c[it] = Pcm<S>::load_vec(m.w2 + s);
             } else {
-                a[it] = load4(m.w1, s, m.n1, m.al1);
-                if (m.mix) c[it] = load4(m.w2, s, m.nmin, m.al2);
+                a[it] = load4<S>(m.w1, s, m.n1, m.al1);
+                if (m.mix) c[it] = load4<S>(m.w2, s, m.nmin, m.al2);
             }
         }
     }
 }
 
-template <bool EXACT, int U0, int U1, bool FULL, int NIT>
-__device__ __forceinline__ void stage_commit(const MixState& m, int S0, int lane, float pe, float c1, const float4 (&a)[NIT],
-                                             const float4 (&c)[NIT], float* __restrict__ D, float* __restrict__ BS,
-                                             float* __restrict__ XS, float& carry) {
+template <bool EXACT, int U0, int U1, bool FULL, class S, int NIT>
+__device__ __forceinline__ void stage_commit(const MixState<S>& m, int S0, int lane, float pe, float c1,
+                                             const typename Pcm<S>::reg_t (&a)[NIT], const typename Pcm<S>::reg_t (&c)[NIT],
+                                             float* __restrict__ D, float* __restrict__ BS, float* __restrict__ XS, float& carry) {
     using Geo = StageGeom<U0, U1>;
     float last_w = 0.f;
 #pragma unroll
@@ -353,11 +396,12 @@ __device__ __forceinline__ void stage_commit(const MixState& m, int S0, int lane
         const int u = U0 + 4 * L;
         const int s = S0 + u;
         const bool in = ((it + 1) * 32 <= Geo::kFloat4) || L < Geo::kFloat4;
+        const float4 fa = Pcm<S>::to_float4(a[it]), fc = Pcm<S>::to_float4(c[it]);
         float4 x;
-        x.x = mix_sample<EXACT, FULL>(m, a[it].x, c[it].x, s);
-        x.y = mix_sample<EXACT, FULL>(m, a[it].y, c[it].y, s + 1);
-        x.z = mix_sample<EXACT, FULL>(m, a[it].z, c[it].z, s + 2);
-        x.w = mix_sample<EXACT, FULL>(m, a[it].w, c[it].w, s + 3);
+        x.x = mix_sample<EXACT, FULL>(m, fa.x, fc.x, s);
+        x.y = mix_sample<EXACT, FULL>(m, fa.y, fc.y, s + 1);
+        x.z = mix_sample<EXACT, FULL>(m, fa.z, fc.z, s + 2);
+        x.w = mix_sample<EXACT, FULL>(m, fa.w, fc.w, s + 3);
         float prev = __shfl_up_sync(0xffffffffu, x.w, 1);
         if (lane == 0) prev = carry;
         carry = __shfl_sync(0xffffffffu, x.w, 31);
@@ -654,9 +698,9 @@ constexpr int kStageIters = StageGeom<kOverlapSamples, kGroupSamples>::kIters;  
 // one live group whose window is staged: frame means, pass 1, (shift), pass 2, power, (prefetch), mel, epilogue.
 // Everything it needs beyond the kernel parameters comes from the warp's shared-memory state (CS_*).  The prefetch
 // leaves the next group's 640 new samples in ra / rc; the caller commits them at the top of its next step.
-template <bool MELSPEC>
-__device__ __forceinline__ void process_group(const StreamParams& p, const float* TAB, float* WS, int lane, float4 (&ra)[kStageIters],
-                                              float4 (&rc)[kStageIters]) {
+template <bool MELSPEC, class S>
+__device__ __forceinline__ void process_group(const StreamParams& p, const float* TAB, float* WS, int lane,
+                                              typename Pcm<S>::reg_t (&ra)[kStageIters], typename Pcm<S>::reg_t (&rc)[kStageIters]) {
     float* D = WS + kWsD;
     float* BS = WS + kWsBS;
     float* XS = WS + kWsXS;
@@ -694,7 +738,7 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
     {
         const int4 ls = cs_q(cs, CS_B);  // b, g, budget, next
         if (ls.w & kNextLive) {  // prefetch the next group's 640 new samples; they are consumed after the epilogue
-            const MixState m = load_mix(cs, p.wav);
+            const MixState<S> m = load_mix<S>(cs, p.wav);
             const int S1 = (ls.y + 1) * kStepSamples;
             if (ls.w & kNextFull) stage_issue<kOverlapSamples, kGroupSamples, true>(m, S1, lane, ra, rc);
             else stage_issue<kOverlapSamples, kGroupSamples, false>(m, S1, lane, ra, rc);
@@ -727,7 +771,7 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
 // Kernel 2: the streaming kernel.  grid = one CTA per SM, block = 16 warps, no CTA barrier after the table load.
 // Warp r of W owns the groups whose preceding cost lies in [r*C/W, (r+1)*C/W)  (clip-major order).
 // ------------------------------------------------------------------------------------------------
-template <bool EXACT, bool MELSPEC, bool PMETA>
+template <bool EXACT, bool MELSPEC, bool PMETA, class S>
 __global__ void __launch_bounds__(kThreads, 1)
     fbank_stream_kernel(const __grid_constant__ StreamParams p, const __grid_constant__ std::conditional_t<PMETA, MetaBlock, MetaNone> meta) {
     using MS = std::conditional_t<PMETA, ParamMeta, GlobalMeta>;
@@ -774,7 +818,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
     int loaded_b = -1;
     bool staged = false;  // the current group's overlap samples are in the window and its new samples in ra / rc
-    float4 ra[kStageIters], rc[kStageIters];
+    typename Pcm<S>::reg_t ra[kStageIters], rc[kStageIters];
     if (p.trace) trace_mark(cs, lane);
 
     while (true) {
@@ -805,7 +849,7 @@ __global__ void __launch_bounds__(kThreads, 1)
         if (p.trace) trace_count(p, cs, lane, staged ? CS_TR_LIVE : CS_TR_COLD, 1);
         bool next_live;
         {
-            MixState m = load_mix(cs, p.wav);
+            MixState<S> m = load_mix<S>(cs, p.wav);
             const int S0 = g * kStepSamples;
             const bool full = window_full(m, S0);
             float* D = WS + kWsD;
@@ -814,11 +858,11 @@ __global__ void __launch_bounds__(kThreads, 1)
             float carry;
             if (!staged) {  // cold start of a run of groups: the whole window is loaded here, nothing was prefetched
                 constexpr int NH = StageGeom<0, kOverlapSamples>::kIters;
-                float4 ha[NH], hc[NH];
+                typename Pcm<S>::reg_t ha[NH], hc[NH];
                 float a0 = 0.f, c0 = 0.f;
                 if (!EXACT) {  // the constant removed from the clip (see mix_sample): its first sample(s)
-                    a0 = __ldg(m.w1);
-                    if (m.mix) c0 = __ldg(m.w2);
+                    a0 = Pcm<S>::load1(m.w1);
+                    if (m.mix) c0 = Pcm<S>::load1(m.w2);
                 }
                 if (full) {
                     stage_issue<0, kOverlapSamples, true>(m, S0, lane, ha, hc);
@@ -850,7 +894,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             }
         }
         __syncwarp();
-        process_group<MELSPEC>(p, TAB, WS, lane, ra, rc);
+        process_group<MELSPEC, S>(p, TAB, WS, lane, ra, rc);
         staged = next_live;
         {  // advance (CS_B / CS_G are read by process_group, so they move only now)
             const int4 l2 = cs_q(cs, CS_B);

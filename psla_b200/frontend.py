@@ -24,8 +24,9 @@ SAMPLE_RATE = 16000
 
 @dataclass
 class PackedWaves:
-    """Waveforms packed back to back in one fp32 buffer; every start is 16-byte aligned."""
-    wav: torch.Tensor  # 1-D float32 (cuda, or pinned / pageable host memory)
+    """Waveforms packed back to back in one buffer, every start a multiple of 4 samples: fp32 in [-1, 1] (what
+    torchaudio.load returns) or int16 PCM (what the wav file holds; the kernel scales by 1 / 32768 like the decoder)."""
+    wav: torch.Tensor  # 1-D float32 or int16 (cuda, or pinned / pageable host memory)
     offsets: np.ndarray  # int64 [n_wav]; waveform i = wav[offsets[i] : offsets[i] + lengths[i]]
     lengths: np.ndarray  # int64 [n_wav]
 
@@ -36,22 +37,29 @@ class PackedWaves:
 
 def pack_waveforms(waves: Sequence[torch.Tensor], device: Union[str, torch.device, None] = None,
                    pinned: bool = False) -> PackedWaves:
-    """Pack [1, n] / [n] fp32 waveforms (channel 0, as kaldi.fbank selects it, kaldi.py:136) with each start
-    rounded up to a multiple of 4 samples so the kernels can use 128-bit loads."""
+    """Pack [1, n] / [n] waveforms (channel 0, as kaldi.fbank selects it, kaldi.py:136) with each start rounded up to
+    a multiple of 4 samples so the kernels can use vector loads.  All-int16 input is packed as int16 PCM, anything else
+    as fp32."""
     lens = np.array([int(w.shape[-1]) for w in waves], dtype=np.int64)
     starts = np.zeros(len(waves), dtype=np.int64)
     pos = 0
     for i, n in enumerate(lens):
         starts[i] = pos
         pos += (int(n) + 3) // 4 * 4
-    flat = torch.zeros(max(pos, 4), dtype=torch.float32, pin_memory=pinned)
+    dtype = torch.int16 if len(waves) > 0 and all(w.dtype == torch.int16 for w in waves) else torch.float32
+    flat = torch.zeros(max(pos, 8), dtype=dtype, pin_memory=pinned)
     for i, w in enumerate(waves):
         w = w.detach()
         w = w[0] if w.dim() == 2 else w
-        flat[starts[i]:starts[i] + lens[i]] = w.to(torch.float32)
+        flat[starts[i]:starts[i] + lens[i]] = w.to(dtype)
     if device is not None:
         flat = flat.to(device, non_blocking=pinned)
     return PackedWaves(flat, starts, lens)
+
+
+def to_pcm16(wave: torch.Tensor) -> torch.Tensor:
+    """fp32 waveform in [-1, 1) -> the int16 PCM a 16-bit wav file of it holds (round to nearest, saturate)."""
+    return torch.clamp(torch.round(wave.to(torch.float32) * 32768.0), -32768, 32767).to(torch.int16)
 
 
 def _as_c(arr: Optional[np.ndarray], dtype, ctype):
@@ -216,7 +224,10 @@ class GpuFbankFrontend:
         am, pm = _as_c(None if masks is None else np.asarray(masks).reshape(B, 4), np.int32, ctypes.c_int32)
         ws = self._workspace(B)
         stream = torch.cuda.current_stream(self.device).cuda_stream
-        st = self.lib.psla_frontend_forward(
+        if wav.dtype not in (torch.float32, torch.int16):
+            raise ValueError("waveforms must be float32 or int16 PCM")
+        fwd = self.lib.psla_frontend_forward_pcm16 if wav.dtype == torch.int16 else self.lib.psla_frontend_forward
+        st = fwd(
             self._h, wav.data_ptr(), p_off, p_len, packed.n_wav, p1, p2, pl, pm, B, T,
             self.norm_mean, self.norm_div, int(self.skip_norm), out.data_ptr(), ws.data_ptr(), ws.numel(), stream)
         _lib.check(st, "psla_frontend_forward", self._h)
@@ -245,7 +256,10 @@ class GpuFbankFrontend:
             if tuple(out_host.shape) != (B, T, self.num_mel_bins) or out_host.dtype != torch.float32 or out_host.is_cuda:
                 raise ValueError("out_host must be a host float32 [B, T, F] tensor")
             out_ptr = out_host.data_ptr()
-        st = self.lib.psla_frontend_forward_host(
+        if wav.dtype not in (torch.float32, torch.int16):
+            raise ValueError("waveforms must be float32 or int16 PCM")
+        fwd = self.lib.psla_frontend_forward_host_pcm16 if wav.dtype == torch.int16 else self.lib.psla_frontend_forward_host
+        st = fwd(
             self._h, wav.data_ptr(), p_off, p_len, packed.n_wav, p1, p2, pl, pm, B, T,
             self.norm_mean, self.norm_div, int(self.skip_norm), out_ptr, s)
         _lib.check(st, "psla_frontend_forward_host", self._h)

@@ -26,7 +26,7 @@ def lib():
 
 def test_library_exports_every_declared_symbol(lib):
     header = open(os.path.join(ROOT, "include", "psla_frontend.h")).read()
-    declared = set(re.findall(r"\b(psla_[a-z_]+)\s*\(", header))
+    declared = set(re.findall(r"\b(psla_[a-z0-9_]+)\s*\(", header))
     declared -= {"psla_frontend_t"}
     assert declared == set(_lib.SYMBOLS), declared ^ set(_lib.SYMBOLS)
     for name in declared:

@@ -222,6 +222,39 @@ def test_deterministic_and_batch_independent(fe):
     assert torch.equal(c[0], a[2])
 
 
+def test_pcm16_input_equals_decoded_float_input(fe):
+    """16-bit PCM as it sits in a wav file -> same bits as the fp32 entry point fed with the decoder's floats
+    (torchaudio.load: value / 32768; audioset_dataset.py:91,95-96), on the device and the host entry points, and the
+    reference's fp32 path on those floats within the tolerance."""
+    from psla_b200.frontend import pack_waveforms, to_pcm16
+    lens = [160000, 100000, 200000, 5003, 400, 48001]
+    pcm = [to_pcm16(synth_wave(500 + i, n, ("gauss", "am", "int16")[i % 3])) for i, n in enumerate(lens)]
+    flt = [w.to(torch.float32) / 32768.0 for w in pcm]
+    src1 = [0, 1, 2, 0, 3, 4, 5, 1]
+    src2 = [-1, 0, 1, 2, -1, -1, 0, 5]   # equal / longer / shorter partners (the latter need the statistics pass)
+    lam = [0.0, 0.3, 0.55, 0.7, 0.0, 0.0, 0.45, 0.62]
+    masks = [(0, 0, 0, 0), (10, 20, 100, 150), (0, 47, 900, 156), (127, 1, 0, 1), (50, 0, 500, 0), (3, 5, 2, 3), (0, 0, 0, 0),
+             (100, 28, 1055, 1)]
+    a = fe(pcm, src1, src2, lam, masks).cpu()
+    b = fe(flt, src1, src2, lam, masks).cpu()
+    assert torch.equal(a, b)
+    ref = O.batch_torch(flt, src1, src2, lam, masks, 1056, MEAN, STD)
+    _check(a, ref, fill=_fill())
+    host = pack_waveforms(pcm, pinned=True)
+    assert host.wav.dtype == torch.int16
+    out_host = torch.empty(len(src1), 1056, 128, pin_memory=True)
+    fe.forward_host(host, np.array(src1, np.int32), np.array(src2, np.int32), np.array(lam), np.array(masks, np.int32), out_host=out_host)
+    torch.cuda.synchronize()
+    assert torch.equal(out_host, a)
+    # unaligned starts inside one shared buffer (scalar load path)
+    flat = torch.cat([torch.zeros(3, dtype=torch.int16), pcm[0][0], torch.zeros(2, dtype=torch.int16), pcm[1][0]]).to(fe.device)
+    from psla_b200.frontend import PackedWaves
+    pk = PackedWaves(flat, np.array([3, 3 + lens[0] + 2], np.int64), np.array(lens[:2], np.int64))
+    c = fe.forward_packed(pk, np.array([0, 1], np.int32), np.array([-1, 0], np.int32), np.array([0.0, 0.3])).cpu()
+    d = fe(flt[:2], [0, 1], [-1, 0], [0.0, 0.3]).cpu()
+    assert torch.equal(c, d)
+
+
 def test_launch_plumbing_does_not_change_results(fe):
     """Descriptors as kernel parameters vs uploaded, launch overlap, copy stream, cost model: identical bits.  A batch
     above the 128-clip parameter-space limit (upload path) equals the same clips computed in small batches."""

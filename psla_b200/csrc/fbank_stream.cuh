@@ -127,7 +127,7 @@ constexpr int kMelSpec0 = 2, kMelSpec1 = 3, kMelSpec2 = 6, kMelSpec3 = 10;
 PSLA_HD void pair_pass1(int n2, int h, const float* __restrict__ D, const float* __restrict__ XS,
                         const float* __restrict__ WINT, const float* __restrict__ TWZ, float* __restrict__ EX,
                         float cmu_x, float cmu_y) {
-    float re[32], im[32];
+    cf z[32];
     {
         // element n1 of the run sits at dx[16*n1 + (n1 >= 20 ? 16 : 0)]; x frame: n1 = 0..24, y frame: n1 = 10..34
         const float* dx = D + 336 * h + n2;
@@ -148,23 +148,19 @@ PSLA_HD void pair_pass1(int n2, int h, const float* __restrict__ D, const float*
         const float vy0 = y0p[0];
         static_for<0, 25>([&](auto n1_) {
             constexpr int n1 = decltype(n1_)::value;
-            re[n1] = (v[n1] - cmu_x) * w[n1];
-            im[n1] = ((n1 == 0 ? vy0 : v[n1 + 10]) - cmu_y) * w[n1];
+            z[n1].x = (v[n1] - cmu_x) * w[n1];
+            z[n1].y = ((n1 == 0 ? vy0 : v[n1 + 10]) - cmu_y) * w[n1];
         });
     }
-    fft_dit<32, 5, 25>(re, im);  // inputs n1 >= 25 are zero (400 = 25 * 16)
+    fft_dit<32, 5, 25>(z);  // inputs n1 >= 25 are zero (400 = 25 * 16)
     float zr, zi;
     ld2(TWZ + 2 * n2, zr, zi);
     static_for<0, 32>([&](auto r_) {
         constexpr int r = decltype(r_)::value;
         constexpr int k1 = brev<5>(r);
-        float ar = re[r], ai = im[r];
-        if constexpr (k1 == 0) {  // row 0 is read by lane 0 of pass 2, whose table row is W_32^n2: compensate
-            const float t = ar * zr - ai * zi;
-            ai = ar * zi + ai * zr;
-            ar = t;
-        }
-        st2(EX + k1 * kExRowFloats + 2 * n2, ar, ai);
+        cf a = z[r];
+        if constexpr (k1 == 0) a = cmul(a, zr, zi);  // row 0 is read by lane 0 of pass 2, whose table row is W_32^n2: compensate
+        st2(EX + k1 * kExRowFloats + 2 * n2, a.x, a.y);
     });
 }
 
@@ -173,8 +169,7 @@ PSLA_HD void pair_pass1(int n2, int h, const float* __restrict__ D, const float*
 //   a[brev4(k2)]            = Z[ka + 32*k2]
 //   b[brev4((k2 + 1) % 16)] = Z[kb + 32*k2]      (the W_16^n2 modulation rotates the output index)
 // ---------------------------------------------------------------------------------------------
-PSLA_HD void pair_pass2_fft(int t, const float* __restrict__ EX, const float* __restrict__ TW, float (&ar)[16],
-                            float (&ai)[16], float (&br)[16], float (&bi)[16]) {
+PSLA_HD void pair_pass2_fft(int t, const float* __restrict__ EX, const float* __restrict__ TW, cf (&a)[16], cf (&b)[16]) {
     const int ka = t;
     const int kb = (t != 0) ? 32 - t : 16;
     const float* ra = EX + ka * kExRowFloats;
@@ -182,30 +177,22 @@ PSLA_HD void pair_pass2_fft(int t, const float* __restrict__ EX, const float* __
     const float* tw = TW + t * kExRowFloats;
     static_for<0, 8>([&](auto q_) {
         constexpr int n = 2 * decltype(q_)::value;
-        ld4(ra + 2 * n, ar[n], ai[n], ar[n + 1], ai[n + 1]);
-        ld4(rb + 2 * n, br[n], bi[n], br[n + 1], bi[n + 1]);
+        ld4(ra + 2 * n, a[n].x, a[n].y, a[n + 1].x, a[n + 1].y);
+        ld4(rb + 2 * n, b[n].x, b[n].y, b[n + 1].x, b[n + 1].y);
     });
     static_for<0, 8>([&](auto q_) {
         constexpr int n = 2 * decltype(q_)::value;
         float w0r, w0i, w1r, w1i;
         ld4(tw + 2 * n, w0r, w0i, w1r, w1i);
         if constexpr (n != 0) {  // TW[t][0] == 1
-            const float xr = ar[n] * w0r - ai[n] * w0i;
-            ai[n] = ar[n] * w0i + ai[n] * w0r;
-            ar[n] = xr;
-            const float yr = br[n] * w0r + bi[n] * w0i;
-            bi[n] = bi[n] * w0r - br[n] * w0i;
-            br[n] = yr;
+            a[n] = cmul(a[n], w0r, w0i);
+            b[n] = cmul_conj(b[n], w0r, w0i);
         }
-        const float xr = ar[n + 1] * w1r - ai[n + 1] * w1i;
-        ai[n + 1] = ar[n + 1] * w1i + ai[n + 1] * w1r;
-        ar[n + 1] = xr;
-        const float yr = br[n + 1] * w1r + bi[n + 1] * w1i;
-        bi[n + 1] = bi[n + 1] * w1r - br[n + 1] * w1i;
-        br[n + 1] = yr;
+        a[n + 1] = cmul(a[n + 1], w1r, w1i);
+        b[n + 1] = cmul_conj(b[n + 1], w1r, w1i);
     });
-    fft_dit<16, 4>(ar, ai);
-    fft_dit<16, 4>(br, bi);
+    fft_dit<16, 4>(a);
+    fft_dit<16, 4>(b);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -219,8 +206,7 @@ PSLA_HD void pair_pass2_fft(int t, const float* __restrict__ EX, const float* __
 // Separate from 2a because P aliases the exchange buffers: every lane of the warp must have finished its pass-2 reads
 // before any lane stores (__syncwarp on the device, loop order on the host).
 // ---------------------------------------------------------------------------------------------
-PSLA_HD void pair_power_store(int t, int h, const float (&ar)[16], const float (&ai)[16], const float (&br)[16],
-                              const float (&bi)[16], float* __restrict__ P) {
+PSLA_HD void pair_power_store(int t, int h, const cf (&a)[16], const cf (&b)[16], float* __restrict__ P) {
     const bool t0 = (t == 0);
     float* plo = P + 4 * t + 2 * h;                          // bin t + 32*k2
     float* phi = P + 4 * (t0 ? 16 : 32 - t) + 2 * h;         // bin hibase + 32*(15-k2)
@@ -228,24 +214,22 @@ PSLA_HD void pair_power_store(int t, int h, const float (&ar)[16], const float (
         constexpr int k2 = decltype(k2_)::value;
         constexpr int ia = brev<4>(k2);              // A[k2]
         constexpr int ib = brev<4>((16 - k2) % 16);  // B[(16-k2) % 16]
-        float ur, ui, vr, vi;
+        cf u, v;
         if constexpr (k2 < 8) {
-            ur = ar[ia];
-            ui = ai[ia];
+            u = a[ia];
             constexpr int ia2 = brev<4>((16 - k2) % 16);  // lane 0: A[(16-k2) % 16]
-            vr = t0 ? ar[ia2] : br[ib];
-            vi = t0 ? ai[ia2] : bi[ib];
+            v.x = t0 ? a[ia2].x : b[ib].x;
+            v.y = t0 ? a[ia2].y : b[ib].y;
         } else {
             constexpr int ib2 = brev<4>((k2 + 1) % 16);  // lane 0: B[(k2+1) % 16]
-            ur = t0 ? br[ib2] : ar[ia];
-            ui = t0 ? bi[ib2] : ai[ia];
-            vr = br[ib];
-            vi = bi[ib];
+            u.x = t0 ? b[ib2].x : a[ia].x;
+            u.y = t0 ? b[ib2].y : a[ia].y;
+            v = b[ib];
         }
-        const float xr = ur + vr, xi = ui - vi;
-        const float yr = ui + vi, yi = vr - ur;
-        const float px = xr * xr + xi * xi;
-        const float py = yr * yr + yi * yi;
+        const cf x = cadd(u, conj_(v));  // X = u + conj(v)
+        const cf y = csub(u, conj_(v));  // i*Y = u - conj(v)
+        const float px = fmaf(x.x, x.x, x.y * x.y);
+        const float py = fmaf(y.x, y.x, y.y * y.y);
         if constexpr (k2 < 8) st2(plo + 128 * k2, px, py);
         else st2(phi + 128 * (15 - k2), px, py);
     });
@@ -264,22 +248,20 @@ struct MelView {
 
 template <int R, int OFF>
 PSLA_HD void mel_slot_static(int lane, const float* __restrict__ P, const float* __restrict__ w, int start, float (&acc)[kGroupFrames]) {
-    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    cf a01 = mk(0.f, 0.f), a23 = mk(0.f, 0.f);  // frames (0, 1) and (2, 3): one two-wide FMA each per tap
     const float* p = P + 4 * start;
     static_for<0, R>([&](auto r_) {
         constexpr int r = decltype(r_)::value;
         const float wv = w[32 * (OFF + r) + lane];
-        float p0, p1, p2, p3;
-        ld4(p + 4 * r, p0, p1, p2, p3);
-        a0 = fmaf(wv, p0, a0);
-        a1 = fmaf(wv, p1, a1);
-        a2 = fmaf(wv, p2, a2);
-        a3 = fmaf(wv, p3, a3);
+        cf p01, p23;
+        ld4(p + 4 * r, p01.x, p01.y, p23.x, p23.y);
+        a01 = cfma(p01, bc(wv), a01);
+        a23 = cfma(p23, bc(wv), a23);
     });
-    acc[0] = a0;
-    acc[1] = a1;
-    acc[2] = a2;
-    acc[3] = a3;
+    acc[0] = a01.x;
+    acc[1] = a01.y;
+    acc[2] = a23.x;
+    acc[3] = a23.y;
 }
 
 template <bool SPEC>

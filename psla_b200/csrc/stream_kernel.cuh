@@ -728,10 +728,10 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
     {
         // pass 2 re-maps the lanes: pair h2 = lane & 1, row t = lane >> 1 (see kExSecondPair)
         const int h2 = lane & 1, t = lane >> 1;
-        float ar[16], ai[16], br[16], bi[16];
-        pair_pass2_fft(t, EX + h2 * kExSecondPair, TAB + kTabTw, ar, ai, br, bi);
+        cf za[16], zb[16];
+        pair_pass2_fft(t, EX + h2 * kExSecondPair, TAB + kTabTw, za, zb);
         __syncwarp();  // P aliases EX: all reads done before any write
-        pair_power_store(t, h2, ar, ai, br, bi, EX);
+        pair_power_store(t, h2, za, zb, EX);
     }
     __syncwarp();
     if (p.trace) trace_phase(p, cs, lane, 7);

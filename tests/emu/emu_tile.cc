@@ -84,18 +84,18 @@ int emu_fbank(const float* x, int n, int num_bins, const float* mel_dense, const
             }
             cmu[f] = c1 * (part[0] * (1.0f / kFrameLen));
         }
-        float regs[32][4][16];
+        cf regs[32][2][16];
         for (int lane = 0; lane < 32; ++lane) {  // pass 1
             const int h = lane >> 4, n2 = lane & 15;
             pair_pass1(n2, h, D, XS, TAB + kTabWin, TAB + kTabTwz, EX + h * kExSecondPair, cmu[2 * h], cmu[2 * h + 1]);
         }
         for (int lane = 0; lane < 32; ++lane) {  // pass 2a (reads)   -- __syncwarp --
             const int h = lane & 1, t = lane >> 1;
-            pair_pass2_fft(t, EX + h * kExSecondPair, TAB + kTabTw, regs[lane][0], regs[lane][1], regs[lane][2], regs[lane][3]);
+            pair_pass2_fft(t, EX + h * kExSecondPair, TAB + kTabTw, regs[lane][0], regs[lane][1]);
         }
         for (int lane = 0; lane < 32; ++lane) {  // pass 2b (P aliases EX) -- __syncwarp --
             const int h = lane & 1, t = lane >> 1;
-            pair_power_store(t, h, regs[lane][0], regs[lane][1], regs[lane][2], regs[lane][3], EX);
+            pair_power_store(t, h, regs[lane][0], regs[lane][1], EX);
         }
         for (int lane = 0; lane < 32; ++lane) {  // mel                    -- __syncwarp --
             float acc[kMelSlots][kGroupFrames];
@@ -135,19 +135,19 @@ void emu_layout(int* v) {
 // inputs 25..31 are ignored / treated as zero)
 void emu_fft(int n, const float* in_re, const float* in_im, float* out_re, float* out_im) {
     if (n == 32 || n == -32) {
-        float re[32], im[32];
-        for (int i = 0; i < 32; ++i) { re[i] = in_re[i]; im[i] = in_im[i]; }
-        if (n == 32) fft_dit<32, 5>(re, im);
+        cf z[32];
+        for (int i = 0; i < 32; ++i) z[i] = mk(in_re[i], in_im[i]);
+        if (n == 32) fft_dit<32, 5>(z);
         else {
-            for (int i = 25; i < 32; ++i) re[i] = im[i] = 0.f;
-            fft_dit<32, 5, 25>(re, im);
+            for (int i = 25; i < 32; ++i) z[i] = mk(0.f, 0.f);
+            fft_dit<32, 5, 25>(z);
         }
-        for (int r = 0; r < 32; ++r) { out_re[brev<5>(r)] = re[r]; out_im[brev<5>(r)] = im[r]; }
+        for (int r = 0; r < 32; ++r) { out_re[brev<5>(r)] = z[r].x; out_im[brev<5>(r)] = z[r].y; }
     } else {
-        float re[16], im[16];
-        for (int i = 0; i < 16; ++i) { re[i] = in_re[i]; im[i] = in_im[i]; }
-        fft_dit<16, 4>(re, im);
-        for (int r = 0; r < 16; ++r) { out_re[brev<4>(r)] = re[r]; out_im[brev<4>(r)] = im[r]; }
+        cf z[16];
+        for (int i = 0; i < 16; ++i) z[i] = mk(in_re[i], in_im[i]);
+        fft_dit<16, 4>(z);
+        for (int r = 0; r < 16; ++r) { out_re[brev<4>(r)] = z[r].x; out_im[brev<4>(r)] = z[r].y; }
     }
 }
 }

@@ -47,6 +47,7 @@ struct psla_frontend {
     int tab_floats = 0;
     size_t smem_bytes = 0;
     int fast_log = 0;
+    float lg2_eps = -23.0f;  // what the device's lg2.approx returns for the float epsilon (probed once in create())
     int exact_mean = 0;
     bool mel_spec = false;
     int num_sms = 0;
@@ -115,6 +116,17 @@ struct DeviceGuard {
     } while (0)
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+__global__ void probe_lg2_kernel(float x, float* out) { *out = lg2_ftz(x); }
+int probe_lg2_eps(psla_frontend* h) {
+    float* d = nullptr;
+    PSLA_CUDA(h, cudaMalloc(&d, sizeof(float)));
+    probe_lg2_kernel<<<1, 1>>>(1.1920928955078125e-07f, d);
+    cudaError_t e = cudaMemcpy(&h->lg2_eps, d, sizeof(float), cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    PSLA_CUDA(h, e);
+    return PSLA_OK;
+}
 
 template <bool EXACT, bool MELSPEC, bool PMETA, class S>
 cudaError_t prepare_one(size_t smem) {
@@ -230,6 +242,7 @@ int psla_frontend_create(psla_frontend_t** handle, int device, int sample_rate, 
         return PSLA_E_CUDA;
     }
     int st = upload_tables(h);
+    if (st == PSLA_OK) st = probe_lg2_eps(h);
     if (st == PSLA_OK) {
         for (auto& s : h->slots)
             if (cudaEventCreateWithFlags(&s.copied, cudaEventDisableTiming) != cudaSuccess ||
@@ -563,6 +576,7 @@ int forward_any(psla_frontend_t* h, const void* wav, bool pcm16, const int64_t* 
     p.nmel = h->nmel;
     p.norm_mean = norm_mean;
     p.norm_div = norm_div;
+    int fast_log = 0;
     // the value every masked / padded cell takes: (0 - mean) / std evaluated like torch does (fp32 sub, IEEE div);
     // likewise the value of a cell on the log floor, log(max(e, eps)) with e <= eps
     {
@@ -574,9 +588,24 @@ int forward_any(psla_frontend_t* h, const void* wav, bool pcm16, const int64_t* 
         const double ln2 = 0.693147180559945309417;
         p.log_scale = skip_norm ? static_cast<float>(ln2) : static_cast<float>(ln2 / static_cast<double>(norm_div));
         p.log_bias = skip_norm ? 0.0f : static_cast<float>(-static_cast<double>(norm_mean) / static_cast<double>(norm_div));
+        // The fast-log epilogue has no select for cells on the floor: nudge the bias (by a few ulps, ~1e-7) until
+        // lg2(eps) * scale + bias (lg2(eps) as the device's lg2.approx returns it, probed in create()) is bit for bit the
+        // reference's value.
+        fast_log = h->fast_log;
+        if (fast_log) {
+            float up = p.log_bias, dn = p.log_bias;
+            bool found = false;
+            for (int k = 0; k < 64 && !found; ++k) {
+                if (fmaf(h->lg2_eps, p.log_scale, up) == p.floor_val) { p.log_bias = up; found = true; }
+                else if (fmaf(h->lg2_eps, p.log_scale, dn) == p.floor_val) { p.log_bias = dn; found = true; }
+                up = nextafterf(up, INFINITY);
+                dn = nextafterf(dn, -INFINITY);
+            }
+            if (!found) fast_log = 0;  // no such bias (never seen): the logf path evaluates the reference's expression verbatim
+        }
     }
     p.skip_norm = skip_norm ? 1 : 0;
-    p.fast_log = h->fast_log;
+    p.fast_log = fast_log;
     p.preemph = h->preemph;
     p.c1 = static_cast<float>(1.0 - static_cast<double>(h->preemph));
     p.cm = h->cm;

@@ -332,18 +332,43 @@ __device__ __forceinline__ bool window_full(const MixState<S>& m, int S0) {
     return m.al1 && S0 + kGroupSamples <= m.n1 && (!m.mix || (m.al2 && S0 + kGroupSamples <= m.nmin));
 }
 
-template <bool EXACT, bool FULL, class S>
-__device__ __forceinline__ float mix_sample(const MixState<S>& m, float a, float c, int s) {
+template <bool FULL, class S>
+__device__ __forceinline__ float mix_sample_exact(const MixState<S>& m, float a, float c, int s) {
     if (!FULL && s >= m.n1) return 0.f;
-    if (!m.mix) return __fsub_rn(a, m.sub1);
+    const float v1 = __fsub_rn(a, m.sub1);
+    if (!m.mix) return v1;
+    const float v2 = (FULL || s < m.nmin) ? __fsub_rn(c, m.mean2) : 0.f;
+    return __fsub_rn(__fadd_rn(__fmul_rn(m.l1, v1), __fmul_rn(m.l2, v2)), m.mixmean);
+}
+// 4 consecutive samples starting at s.  The fused form is one expression for mixed and plain clips: a plain clip carries
+// l1 = 1, l2 = 0 (enter_clip), and 1*a + (0*c - K) == a - K bit for bit -- two two-wide FMAs per sample pair, no selects.
+template <bool EXACT, bool FULL, class S>
+__device__ __forceinline__ float4 mix4(const MixState<S>& m, const float4& a, float4 c, int s) {
+    float4 x;
     if (EXACT) {
-        const float v1 = __fsub_rn(a, m.sub1);
-        const float v2 = (FULL || s < m.nmin) ? __fsub_rn(c, m.mean2) : 0.f;
-        return __fsub_rn(__fadd_rn(__fmul_rn(m.l1, v1), __fmul_rn(m.l2, v2)), m.mixmean);
-    } else {
-        const float ce = (FULL || s < m.nmin) ? c : m.mean2;
-        return fmaf(m.l1, a, fmaf(m.l2, ce, -m.sub1));
+        x.x = mix_sample_exact<FULL>(m, a.x, c.x, s);
+        x.y = mix_sample_exact<FULL>(m, a.y, c.y, s + 1);
+        x.z = mix_sample_exact<FULL>(m, a.z, c.z, s + 2);
+        x.w = mix_sample_exact<FULL>(m, a.w, c.w, s + 3);
+        return x;
     }
+    if (!FULL) {  // past the partner's end its (removed) mean takes the place of the zero padding
+        c.x = (s < m.nmin) ? c.x : m.mean2;
+        c.y = (s + 1 < m.nmin) ? c.y : m.mean2;
+        c.z = (s + 2 < m.nmin) ? c.z : m.mean2;
+        c.w = (s + 3 < m.nmin) ? c.w : m.mean2;
+    }
+    const cf nk = bc(-m.sub1);
+    const cf lo = cfma(bc(m.l1), mk(a.x, a.y), cfma(bc(m.l2), mk(c.x, c.y), nk));
+    const cf hi = cfma(bc(m.l1), mk(a.z, a.w), cfma(bc(m.l2), mk(c.z, c.w), nk));
+    x = make_float4(lo.x, lo.y, hi.x, hi.y);
+    if (!FULL) {
+        x.x = (s < m.n1) ? x.x : 0.f;
+        x.y = (s + 1 < m.n1) ? x.y : 0.f;
+        x.z = (s + 2 < m.n1) ? x.z : 0.f;
+        x.w = (s + 3 < m.n1) ? x.w : 0.f;
+    }
+    return x;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -397,11 +422,7 @@ __device__ __forceinline__ void stage_commit(const MixState<S>& m, int S0, int l
         const int s = S0 + u;
         const bool in = ((it + 1) * 32 <= Geo::kFloat4) || L < Geo::kFloat4;
         const float4 fa = Pcm<S>::to_float4(a[it]), fc = Pcm<S>::to_float4(c[it]);
-        float4 x;
-        x.x = mix_sample<EXACT, FULL>(m, fa.x, fc.x, s);
-        x.y = mix_sample<EXACT, FULL>(m, fa.y, fc.y, s + 1);
-        x.z = mix_sample<EXACT, FULL>(m, fa.z, fc.z, s + 2);
-        x.w = mix_sample<EXACT, FULL>(m, fa.w, fc.w, s + 3);
+        const float4 x = mix4<EXACT, FULL>(m, fa, fc, s);
         float prev = __shfl_up_sync(0xffffffffu, x.w, 1);
         if (lane == 0) prev = carry;
         carry = __shfl_sync(0xffffffffu, x.w, 31);
@@ -554,7 +575,7 @@ __device__ __forceinline__ void enter_clip(const StreamParams& p, const MS& ms, 
     // (fused mode: CS_SUB1 is filled by the first cold start of the clip, whose loads fetch the first samples anyway)
     __syncwarp();
     if (lane == 0) {
-        cs_set_q(cs, CS_N1, d.n1, nmin, __float_as_int(d.l1), __float_as_int(d.l2));
+        cs_set_q(cs, CS_N1, d.n1, nmin, __float_as_int(mix ? d.l1 : 1.0f), __float_as_int(mix ? d.l2 : 0.0f));
         cs_set_q(cs, CS_SUB1, __float_as_int(sub1), __float_as_int(mean2), __float_as_int(mixmean),
                  (d.flags & (kFlagAligned1 | kFlagAligned2)) | (mix ? kCsMix : 0));
         cs_set_q(cs, CS_OFF1, static_cast<int>(d.off1), static_cast<int>(d.off1 >> 32), static_cast<int>(d.off2), static_cast<int>(d.off2 >> 32));
@@ -580,39 +601,50 @@ template <bool FASTLOG, int NMEL>
 __device__ __forceinline__ void epilogue(const StreamParams& p, const int* cs, const int* mel_bin, int lane, int f0, float* __restrict__ out,
                                          const float (&acc)[kMelSlots][kGroupFrames]) {
     const float eps = 1.1920928955078125e-07f;  // kaldi.py:22
-    const float fill = p.fill, floor_val = p.floor_val, la = p.log_scale, lb = p.log_bias;
+    const float fill = p.fill;
     const int nmel = NMEL ? NMEL : p.nmel;
     const int4 mq = cs_q(cs, CS_F0);
     const int mf0 = mq.x, mf1 = mq.y, t0 = mq.z, t1 = mq.w, m_eff = cs_i(cs, CS_MEFF);
     float* col[kMelSlots];  // the lane's four columns at row f0
     bool keep[kMelSlots];   // column survives the frequency mask
     bool own[kMelSlots];
+    // FASTLOG: value = lg2(max(e, eps)) * la + lb with the frequency mask folded into the constants of the column
+    // (masked: 0 * lg + fill == fill exactly).  The host picks log_bias such that lg2(eps) * la + lb is exactly the
+    // reference's value of a cell on the float-epsilon floor, so floored cells need no select either.
+    float la[kMelSlots], lb[kMelSlots];
 #pragma unroll
     for (int i = 0; i < kMelSlots; ++i) {
         const int mb = mel_bin[32 * i + lane];
         own[i] = NMEL != 0 || mb >= 0;
         keep[i] = !(mb >= mf0 && mb < mf1);
         col[i] = out + static_cast<size_t>(f0) * nmel + max(mb, 0);
+        la[i] = keep[i] ? p.log_scale : 0.f;
+        lb[i] = keep[i] ? p.log_bias : fill;
     }
     const int rows = min(kGroupFrames, p.T - f0);
 #pragma unroll
     for (int q = 0; q < kGroupFrames; ++q) {
         if (q < rows) {  // warp-uniform
             const int row = f0 + q;
-            const bool rlive = row < m_eff && !(row >= t0 && row < t1);
+            const bool rlive = row < m_eff && !(row >= t0 && row < t1);  // warp-uniform
+            if (!rlive) {
 #pragma unroll
-            for (int i = 0; i < kMelSlots; ++i) {
-                const float e = acc[i][q];
-                float v;
-                if (FASTLOG) {  // branch-free: the log of a floored / dead cell is computed and discarded
-                    v = fmaf(lg2_ftz(fmaxf(e, eps)), la, lb);
-                    v = (e > eps) ? v : floor_val;
-                } else {
-                    const float lg = logf(fmaxf(e, eps));
-                    v = p.skip_norm ? lg : __fdiv_rn(__fsub_rn(lg, p.norm_mean), p.norm_div);
+                for (int i = 0; i < kMelSlots; ++i)
+                    if (own[i]) __stcs(col[i] + q * nmel, fill);
+            } else {
+#pragma unroll
+                for (int i = 0; i < kMelSlots; ++i) {
+                    const float e = acc[i][q];
+                    float v;
+                    if (FASTLOG) {
+                        v = fmaf(lg2_ftz(fmaxf(e, eps)), la[i], lb[i]);
+                    } else {
+                        const float lg = logf(fmaxf(e, eps));
+                        v = p.skip_norm ? lg : __fdiv_rn(__fsub_rn(lg, p.norm_mean), p.norm_div);
+                        v = keep[i] ? v : fill;
+                    }
+                    if (own[i]) __stcs(col[i] + q * nmel, v);
                 }
-                v = (rlive && keep[i]) ? v : fill;
-                if (own[i]) __stcs(col[i] + q * nmel, v);
             }
         }
     }

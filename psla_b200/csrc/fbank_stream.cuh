@@ -13,7 +13,7 @@
 //   pass 1   lane n2 (0..15) holds z[16*n1 + n2], n1 = 0..31 (only n1 < 25 is non-zero: 400 = 25*16).  The y frame
 //            starts 160 samples = 10 n1-steps after the x frame, so ONE run of 35 staged values feeds both.
 //            -> 32-point DIT FFT over n1 in registers (FMA-only butterflies, first stage pruned for the 7 zero inputs) -> shared memory
-//            EX[k1][n2], untwiddled (row 0 pre-multiplied by W_32^-n2, see below).
+//            EX[k1][n2], untwiddled (row 0 pre-multiplied by W_32^-n2, see below).  EX aliases the staged samples (kWsEX).
 //   pass 2   lane t reads rows ka = t and kb = 32 - t (lane 0: rows 0 and 16), multiplies row ka by
 //            TW[t][n2] = W_512^(t*n2) and row kb by conj(TW[t][n2]): because W_512^((32-t)*n2) = W_16^n2 * conj(TW[t][n2])
 //            and a modulation by W_16^n2 only rotates the 16-point FFT's output index by one, both rows share one
@@ -92,15 +92,20 @@ constexpr int kExFloats = kExSecondPair + kExPairFloats;  // 2320
 constexpr int kPFloats = 4 * (kNfft / 2);  // bins 0..255 (bin 256 never carries mel weight: kaldi.py:627 pads a zero column)
 static_assert(kPFloats <= kExFloats, "P must fit in the warp's exchange buffers");
 
-// per-warp shared-memory window (floats)
+// per-warp shared-memory window (floats).  The exchange buffers ALIAS the staged samples from sample 256 on: once every
+// lane of the warp holds its pass-1 inputs in registers and the 240 samples shared with the next group have moved to
+// the front (stage_shift), the rest of D is dead until the next step commits its new samples -- by then the power
+// spectra (which alias EX) have been consumed by the mel stage.  10.7 KB per warp instead of 13.3 KB: two CTAs of 8
+// warps fit one SM, so the start-up of one launch overlaps the steady state of its neighbour.
 constexpr int kWsD = 0;
-constexpr int kWsBS = kWsD + kDFloats;
+constexpr int kWsEX = 256;  // >= kOverlapSamples (the part of D that survives the shift), multiple of 32 (same banks)
+constexpr int kWsBS = kWsEX + kExFloats;
 constexpr int kWsXS = kWsBS + kBsFloats;
 constexpr int kWsCS = kWsXS + kXsFloats;  // per-clip state of the warp (kept out of the register file, see stream_kernel.cuh)
 constexpr int kCsWords = 36;
-constexpr int kWsEX = kWsCS + kCsWords;
-constexpr int kWarpFloats = kWsEX + kExFloats;  // 3332 floats = 13328 B
-static_assert((kWsEX * 4) % 16 == 0 && (kWarpFloats * 4) % 16 == 0, "16-byte alignment of vector regions");
+constexpr int kWarpFloats = kWsCS + kCsWords;  // 2676 floats = 10704 B
+static_assert(kWsEX >= kOverlapSamples && kWsEX % 32 == 0 && kWsEX + kExFloats >= kDFloats, "EX aliases the tail of D");
+static_assert((kWsEX * 4) % 16 == 0 && (kWsCS * 4) % 16 == 0 && (kWarpFloats * 4) % 16 == 0, "16-byte alignment of vector regions");
 
 // Constant tables (floats), copied once per CTA into shared memory.
 constexpr int kWinRow = 28;                            // WINT[n2][n1], n1 < 25, zero padded: 0.5 * window[16*n1 + n2]
@@ -125,9 +130,7 @@ constexpr int kMelSpec0 = 2, kMelSpec1 = 3, kMelSpec2 = 6, kMelSpec3 = 10;
 //         (:193-198) commute into  d[j] - (1-p)*mu  (first sample: (1-p)*(x0 - mu), replicate padding)
 // ---------------------------------------------------------------------------------------------
 PSLA_HD void pair_pass1(int n2, int h, const float* __restrict__ D, const float* __restrict__ XS,
-                        const float* __restrict__ WINT, const float* __restrict__ TWZ, float* __restrict__ EX,
-                        float cmu_x, float cmu_y) {
-    cf z[32];
+                        const float* __restrict__ WINT, float cmu_x, float cmu_y, cf (&z)[32]) {
     {
         // element n1 of the run sits at dx[16*n1 + (n1 >= 20 ? 16 : 0)]; x frame: n1 = 0..24, y frame: n1 = 10..34
         const float* dx = D + 336 * h + n2;
@@ -153,6 +156,10 @@ PSLA_HD void pair_pass1(int n2, int h, const float* __restrict__ D, const float*
         });
     }
     fft_dit<32, 5, 25>(z);  // inputs n1 >= 25 are zero (400 = 25 * 16)
+}
+// The stores of pass 1, separate because EX aliases D: every lane of the warp must have read its samples (and the
+// overlap must have been shifted) before any lane stores (__syncwarp on the device, loop order on the host).
+PSLA_HD void pair_pass1_store(int n2, const float* __restrict__ TWZ, float* __restrict__ EX, const cf (&z)[32]) {
     float zr, zi;
     ld2(TWZ + 2 * n2, zr, zi);
     static_for<0, 32>([&](auto r_) {

@@ -34,6 +34,7 @@
 using namespace psla;
 
 constexpr int kMetaSlots = 4;
+constexpr int kCtasPerSm = 2;  // __launch_bounds__(kThreads, 2): 8 warps x 128 registers and ~96 KB of shared memory per CTA
 
 struct psla_frontend {
     int device = 0;
@@ -166,7 +167,7 @@ int upload_tables(psla_frontend* h) {
     if (!build_table_buffer(h->window.data(), h->mel_dense.data(), h->nmel, &buf, &spec)) return PSLA_E_UNSUPPORTED;
     const int total = static_cast<int>(buf.size());
     const size_t smem = (static_cast<size_t>(total) + static_cast<size_t>(kWarpsPerCta) * kWarpFloats) * sizeof(float);
-    if (smem > 227 * 1024) return PSLA_E_UNSUPPORTED;  // tables + 16 warp windows must fit one SM
+    if (kCtasPerSm * (smem + 1024) > 228 * 1024) return PSLA_E_UNSUPPORTED;  // two CTAs (tables + 8 warp windows each) must fit one SM
     if (h->d_tab) {
         PSLA_CUDA(h, cudaDeviceSynchronize());
         cudaFree(h->d_tab);
@@ -343,7 +344,7 @@ int psla_frontend_get_timing(psla_frontend_t* h, double* stats_ms, double* tile_
 
 int psla_frontend_set_trace(psla_frontend_t* h, int64_t* device_buf, size_t capacity_records) {
     if (!h) return PSLA_E_INVALID;
-    const size_t need = static_cast<size_t>(h->num_sms > 0 ? h->num_sms : 148) * kWarpsPerCta;
+    const size_t need = static_cast<size_t>(h->num_sms > 0 ? h->num_sms : 148) * kCtasPerSm * kWarpsPerCta;
     if (device_buf && capacity_records < need) return PSLA_E_WORKSPACE;
     static_assert(sizeof(long long) == sizeof(int64_t), "trace word");
     h->trace = reinterpret_cast<long long*>(device_buf);
@@ -351,7 +352,7 @@ int psla_frontend_set_trace(psla_frontend_t* h, int64_t* device_buf, size_t capa
 }
 
 int psla_frontend_trace_records(const psla_frontend_t* h) {
-    return h ? (h->num_sms > 0 ? h->num_sms : 148) * kWarpsPerCta : 0;
+    return h ? (h->num_sms > 0 ? h->num_sms : 148) * kCtasPerSm * kWarpsPerCta : 0;
 }
 
 int psla_frontend_trace_words(void) { return kTraceWords; }
@@ -621,7 +622,7 @@ int forward_any(psla_frontend_t* h, const void* wav, bool pcm16, const int64_t* 
     h->prev_out_lo = out_lo;
     h->prev_out_hi = out_hi;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(h->num_sms > 0 ? h->num_sms : 148);
+    cfg.gridDim = dim3((h->num_sms > 0 ? h->num_sms : 148) * kCtasPerSm);
     cfg.blockDim = dim3(kThreads);
     cfg.dynamicSmemBytes = h->smem_bytes;
     cfg.stream = stream;

@@ -42,7 +42,7 @@ constexpr CostModel kDefaultCost = {64, 2, 48};
 constexpr int kStatSegs = 8;  // partial sums per clip
 constexpr int kStatVals = 3;  // sum(w1), sum(w2), sum(w2[0:min(n1,n2)])
 
-constexpr int kWarpsPerCta = 16;
+constexpr int kWarpsPerCta = 8;   // two CTAs per SM
 constexpr int kThreads = kWarpsPerCta * 32;
 
 struct StreamParams {
@@ -753,10 +753,18 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
         cmu_x = __shfl_sync(0xffffffffu, cmu, 16 * h);
         cmu_y = __shfl_sync(0xffffffffu, cmu, 16 * h + 8);
     }
-    pair_pass1(n2, h, D, XS, TAB + kTabWin, TAB + kTabTwz, EX + h * kExSecondPair, cmu_x, cmu_y);
+    {
+        cf z[32];
+        pair_pass1(n2, h, D, XS, TAB + kTabWin, cmu_x, cmu_y, z);
+        __syncwarp();  // EX aliases D: every lane has its samples in registers ...
+        if (cs_i(cs, CS_NEXT) & kNextLive) {
+            stage_shift(lane, D, BS, XS);  // ... and the part the next group shares has moved below kWsEX
+            __syncwarp();
+        }
+        pair_pass1_store(n2, TAB + kTabTwz, EX + h * kExSecondPair, z);
+    }
     __syncwarp();
     if (p.trace) trace_phase(p, cs, lane, 6);
-    if (cs_i(cs, CS_NEXT) & kNextLive) stage_shift(lane, D, BS, XS);
     {
         // pass 2 re-maps the lanes: pair h2 = lane & 1, row t = lane >> 1 (see kExSecondPair)
         const int h2 = lane & 1, t = lane >> 1;
@@ -800,11 +808,11 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
 }
 
 // ------------------------------------------------------------------------------------------------
-// Kernel 2: the streaming kernel.  grid = one CTA per SM, block = 16 warps, no CTA barrier after the table load.
+// Kernel 2: the streaming kernel.  grid = two CTAs per SM, block = 8 warps, no CTA barrier after the table load.
 // Warp r of W owns the groups whose preceding cost lies in [r*C/W, (r+1)*C/W)  (clip-major order).
 // ------------------------------------------------------------------------------------------------
 template <bool EXACT, bool MELSPEC, bool PMETA, class S>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, 2)
     fbank_stream_kernel(const __grid_constant__ StreamParams p, const __grid_constant__ std::conditional_t<PMETA, MetaBlock, MetaNone> meta) {
     using MS = std::conditional_t<PMETA, ParamMeta, GlobalMeta>;
     MS ms;

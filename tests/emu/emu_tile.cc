@@ -85,9 +85,14 @@ int emu_fbank(const float* x, int n, int num_bins, const float* mel_dense, const
             cmu[f] = c1 * (part[0] * (1.0f / kFrameLen));
         }
         cf regs[32][2][16];
-        for (int lane = 0; lane < 32; ++lane) {  // pass 1
+        static cf z1[32][32];
+        for (int lane = 0; lane < 32; ++lane) {  // pass 1 (reads D)
             const int h = lane >> 4, n2 = lane & 15;
-            pair_pass1(n2, h, D, XS, TAB + kTabWin, TAB + kTabTwz, EX + h * kExSecondPair, cmu[2 * h], cmu[2 * h + 1]);
+            pair_pass1(n2, h, D, XS, TAB + kTabWin, cmu[2 * h], cmu[2 * h + 1], z1[lane]);
+        }
+        for (int lane = 0; lane < 32; ++lane) {  // pass 1 stores (EX aliases D)   -- __syncwarp --
+            const int h = lane >> 4, n2 = lane & 15;
+            pair_pass1_store(n2, TAB + kTabTwz, EX + h * kExSecondPair, z1[lane]);
         }
         for (int lane = 0; lane < 32; ++lane) {  // pass 2a (reads)   -- __syncwarp --
             const int h = lane & 1, t = lane >> 1;

@@ -33,6 +33,18 @@ WORKLOAD = ("AudioSet training batch: 100 clips x 10 s @16 kHz (150 waveforms), 
             "target_length=1056, 128 mel bins")
 
 
+
+def _claim_stdout():
+    """The driver parses stdout as ONE JSON line: libraries that write to fd 1 (NCCL's version banner under torchrun)
+    are sent to stderr, the JSON line goes to a duplicate of the original stdout."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    return real
+
+
+_JSON_OUT = sys.stdout
+
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -67,7 +79,7 @@ def run_reference(args):
             "cpu_baseline": {"value": r["clips_per_s"], "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]},
             "e2e": {"value": r["clips_per_s"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_JSON_OUT, flush=True)
     return 0
 
 
@@ -311,7 +323,7 @@ def run_b200(args):
                 "gpu_launches": launches, "roofline": roofline, "checksum": checksum}
         if cpu is not None:
             line["cpu_baseline"] = cpu
-        print(json.dumps(line), flush=True)
+        print(json.dumps(line), file=_JSON_OUT, flush=True)
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -319,4 +331,5 @@ def run_b200(args):
 
 if __name__ == "__main__":
     a = parse_args()
+    _JSON_OUT = _claim_stdout()
     sys.exit(run_reference(a) if a.impl == "reference" else run_b200(a))

@@ -139,3 +139,19 @@ def test_frontend_needs_cuda():
     from psla_b200.frontend import GpuFbankFrontend
     with pytest.raises(RuntimeError):
         GpuFbankFrontend({"num_mel_bins": 128, "target_length": 1056, "mean": 0.0, "std": 1.0})
+
+
+def test_long_recording_chunk_offsets():
+    from psla_b200.inference import chunk_offsets
+    s, n = chunk_offsets(57_600_000, 160000)  # one hour at 16 kHz -> 360 windows of 10 s (BASELINE config 4)
+    assert len(s) == 360 and (n == 160000).all() and s[-1] == 359 * 160000
+    s, n = chunk_offsets(3 * 160000 + 7, 160000)  # a 7-sample remainder holds no frame: dropped (kaldi.py:142 would assert)
+    assert s.tolist() == [0, 160000, 320000] and n.tolist() == [160000] * 3
+    s, n = chunk_offsets(3 * 160000 + 500, 160000)  # a remainder with >= 1 frame is a short clip of its own
+    assert s.tolist() == [0, 160000, 320000, 480000] and n.tolist() == [160000] * 3 + [500]
+    s, n = chunk_offsets(500000, 160000, hop=80000)  # overlapping windows: only the first short one is kept
+    assert s.tolist() == [0, 80000, 160000, 240000, 320000, 400000] and n[-1] == 100000
+    assert len(chunk_offsets(399, 160000)[0]) == 0
+    assert len(chunk_offsets(3 * 160000 + 500, 160000, keep_tail=False)[0]) == 3
+    with pytest.raises(ValueError):
+        chunk_offsets(1000, 100)

@@ -395,3 +395,26 @@ def test_dataset_drop_in_matches_reference_getitem(FE, golden_dir):
             _check(feats, ref, div=div, fill=fill)
             assert torch.equal(batch.labels, torch.from_numpy(g["labels"]))
             fe.close()
+
+
+def test_c4_long_recording_chunks_equal_per_clip_oracle(FE):
+    """C4: a long recording cut into 10 s windows; every window is an independent eval clip (own DC removal, no masks)."""
+    from psla_b200.inference import LongRecordingFrontend
+    fe = FE(CONF)
+    n = 6 * 160000 + 12345
+    x = synth_wave(90, n)[0] + 0.02  # DC offset: removed per window, not per recording
+    lr = LongRecordingFrontend(fe, x, window_s=10.0)
+    assert len(lr) == 7 and lr.lengths[-1] == 12345
+    got = torch.cat([f for _, f in lr.batches(3)], dim=0)
+    chunks = [x[s:s + l].unsqueeze(0) for s, l in zip(lr.starts.tolist(), lr.lengths.tolist())]
+    ref = O.batch_torch(chunks, list(range(7)), [-1] * 7, [0.0] * 7, [(0, 0, 0, 0)] * 7, 1056, MEAN, STD)
+    _check(got, ref, fill=_fill(), near_floor_below=-13.0)  # mel bin 0 (one FFT bin, tiny weight) dips to -14.9 in a few frames
+    # batched == one window at a time, bit for bit; overlapping hop reuses the same device buffer
+    one = torch.cat([lr.features(i, i + 1) for i in range(7)], dim=0)
+    assert torch.equal(one, got)
+    lr2 = LongRecordingFrontend(fe, x, window_s=10.0, hop_s=2.5)
+    f2 = lr2.features(0, len(lr2))
+    assert torch.equal(f2[0], got[0]) and torch.equal(f2[4], got[1])  # hop 2.5 s: window 4 starts at 10 s
+    starts, y = lr.predict(lambda f: f.mean(dim=(1, 2)).unsqueeze(1), batch=4)
+    assert y.shape == (7, 1) and starts.tolist() == lr.starts.tolist()
+    fe.close()

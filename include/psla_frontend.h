@@ -100,6 +100,17 @@ int psla_frontend_forward_host_pcm16(psla_frontend_t* handle, const int16_t* wav
                                      const double* lambda, const int32_t* mask, int n_clips, int target_length, float norm_mean,
                                      float norm_div, int skip_norm, float* out_host, void* stream);
 
+/* Replaces: the noise / roll augmentation of audioset_dataset.py:197-199 (`noise == True`; off in every recipe of the
+ * reference, run.py:77,80) for B clips:   out[b][(t + shift[b]) mod T][f] = in[b][t][f] + (noise[b][t][f] * scale[b]) / 10
+ *   in, out   DEVICE  [B][target_length][num_mel_bins] fp32, distinct buffers (a roll cannot run in place)
+ *   noise     DEVICE  the U[0,1) field the host drew with torch.rand(T, F) per clip (:198) -- bit-exact parity -- or NULL:
+ *                     the kernel then draws it itself (Philox-4x32-10 keyed by `seed`, clip and cell; same distribution)
+ *   scale     HOST    [B] fp32(np.random.rand()) per clip (:198)
+ *   shift     HOST    [B] np.random.randint(-10, 10) per clip (:199), any value in (-T, T)
+ * Asynchronous on `stream`; one extra pass over the features (read + write). */
+int psla_frontend_noise_roll(psla_frontend_t* handle, const float* in, float* out, const float* noise, const float* scale,
+                             const int32_t* shift, int n_clips, int target_length, uint64_t seed, void* stream);
+
 /* Number of frames kaldi.fbank produces for n_samples (snip_edges=True, kaldi.py:63-67); < 0 if too short. */
 int psla_frontend_num_frames(const psla_frontend_t* handle, int64_t n_samples);
 /* Kernels launched by this handle since creation (bench.py reports it as gpu_launches). */

@@ -105,11 +105,14 @@ def gen_mask_offsets():
     print("mask_offsets: width ranges", out[:, 1].min(), out[:, 1].max(), out[:, 3].min(), out[:, 3].max())
 
 
-def gen_getitem(AudiosetDataset):
+def gen_getitem(AudiosetDataset, only=None):
     waves = tiny_dataset_waves()
     with tempfile.TemporaryDirectory() as tmp:
         jpath, cpath = write_tiny_dataset(tmp, waves)
         confs = {
+            # the noise / roll augmentation (:197-199), off in every recipe of the reference but part of its dataset API
+            "noise": {"num_mel_bins": 128, "target_length": 96, "freqm": 24, "timem": 40, "mixup": 0.5,
+                      "dataset": "audioset", "mode": "train", "mean": -4.6476, "std": 4.5699, "noise": True},
             "train": {"num_mel_bins": 128, "target_length": 96, "freqm": 24, "timem": 40, "mixup": 0.5,
                       "dataset": "audioset", "mode": "train", "mean": -4.6476, "std": 4.5699, "noise": False},
             "eval": {"num_mel_bins": 128, "target_length": 96, "freqm": 0, "timem": 0, "mixup": 0,
@@ -119,6 +122,8 @@ def gen_getitem(AudiosetDataset):
                          "skip_norm": True},
         }
         for name, conf in confs.items():
+            if only is not None and name not in only:
+                continue
             ds = AudiosetDataset(jpath, audio_conf=conf, label_csv=cpath)
             feats, labels = [], []
             for seed in (0, 1):
@@ -137,6 +142,9 @@ def gen_getitem(AudiosetDataset):
 def main():
     os.makedirs(GOLD, exist_ok=True)
     torch.set_num_threads(1)
+    if len(sys.argv) > 1:  # e.g. `python oracle/gen_golden.py noise`: (re)generate only the named __getitem__ fixtures
+        gen_getitem(import_reference_dataset(), only=set(sys.argv[1:]))
+        return
     gen_fbank_c1()
     gen_tables()
     gen_mask_offsets()

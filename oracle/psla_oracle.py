@@ -307,7 +307,8 @@ def item_torch(waves: Sequence[torch.Tensor], index: int, audio_conf: dict, py_r
     ``psla_b200.dataloaders`` host code) for in-memory waveforms ``waves[i]`` ([1, n_i]).
 
     RNG order: ``random.random()`` (:147), ``random.randint`` (:153), ``np.random.beta`` (:114),
-    then 2 ``torch.rand(1)`` per active mask, freq before time (:182-185)."""
+    then 2 ``torch.rand(1)`` per active mask, freq before time (:182-185); with ``noise``: ``torch.rand(T, F)``,
+    ``np.random.rand()``, ``np.random.randint(-10, 10)`` (:198-199)."""
     mixup = audio_conf.get("mixup")
     T = audio_conf.get("target_length")
     F = audio_conf.get("num_mel_bins")
@@ -322,7 +323,15 @@ def item_torch(waves: Sequence[torch.Tensor], index: int, audio_conf: dict, py_r
     mask = draw_mask_offsets(audio_conf.get("freqm"), audio_conf.get("timem"), F, T)
     skip = bool(audio_conf.get("skip_norm")) if audio_conf.get("skip_norm") else False
     out = apply_masks_and_norm_torch(fb, mask, audio_conf.get("mean"), audio_conf.get("std"), skip)
+    if audio_conf.get("noise") == True:  # noqa: E712  (audioset_dataset.py:197-199)
+        out = noise_roll_torch(out, torch.rand(out.shape[0], out.shape[1]), np_random.rand(), np_random.randint(-10, 10))
     return out, ItemDraw(mixed, partner, lam, mask)
+
+
+def noise_roll_torch(fbank: torch.Tensor, field: torch.Tensor, scale: float, shift: int) -> torch.Tensor:
+    """audioset_dataset.py:198-199 with the three random draws made explicit: `fbank + field * scale / 10`, rolled by
+    `shift` rows along time (torch.roll: row t moves to (t + shift) mod T)."""
+    return torch.roll(fbank + field * scale / 10, int(shift), 0)
 
 
 def batch_torch(waves: Sequence[torch.Tensor], src1: Sequence[int], src2: Sequence[int], lam: Sequence[float],

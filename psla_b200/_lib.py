@@ -35,6 +35,8 @@ SYMBOLS = {
     "psla_frontend_forward_host_pcm16": (c_int, [c_void_p, c_void_p, POINTER(c_int64), POINTER(c_int64), c_int, POINTER(c_int32),
                                                  POINTER(c_int32), POINTER(c_double), POINTER(c_int32), c_int, c_int, c_float, c_float,
                                                  c_int, c_void_p, c_void_p]),
+    "psla_frontend_noise_roll": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, POINTER(c_float), POINTER(c_int32), c_int, c_int,
+                                         ctypes.c_uint64, c_void_p]),
     "psla_frontend_num_frames": (c_int, [c_void_p, c_int64]),
     "psla_frontend_launch_count": (c_int64, [c_void_p]),
     "psla_frontend_set_fast_log": (c_int, [c_void_p, c_int]),

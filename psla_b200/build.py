@@ -8,7 +8,7 @@ import subprocess
 CSRC = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc")
 LIB = os.path.join(CSRC, "libpsla_frontend.so")
 SOURCES = ("psla_frontend.cu", "tables.cc")
-HEADERS = ("fft_core.cuh", "fbank_stream.cuh", "stream_kernel.cuh", "tables.h", os.path.join("..", "..", "include", "psla_frontend.h"))
+HEADERS = ("fft_core.cuh", "fbank_stream.cuh", "stream_kernel.cuh", "noise_roll.cuh", "tables.h", os.path.join("..", "..", "include", "psla_frontend.h"))
 NVCC_FLAGS = ("-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared")
 

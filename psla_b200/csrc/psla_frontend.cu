@@ -25,6 +25,7 @@
 #include <vector>
 
 #include "../../include/psla_frontend.h"
+#include "noise_roll.cuh"
 #include "stream_kernel.cuh"
 #include "tables.h"
 
@@ -306,6 +307,39 @@ size_t psla_frontend_workspace_bytes(const psla_frontend_t* h, int n_clips) {
     const size_t meta = align_up(static_cast<size_t>(n_clips) * sizeof(ClipDesc), 256) +
                         align_up((static_cast<size_t>(n_clips) + 1) * sizeof(ClipCost), 256);
     return kMetaSlots * meta + static_cast<size_t>(n_clips) * kStatSegs * kStatVals * sizeof(double);
+}
+
+int psla_frontend_noise_roll(psla_frontend_t* h, const float* in, float* out, const float* noise, const float* scale,
+                             const int32_t* shift, int n_clips, int target_length, uint64_t seed, void* stream_) {
+    if (!h || !in || !out || !scale || !shift || n_clips < 0 || target_length < 1 || in == out) return PSLA_E_INVALID;
+    if (n_clips == 0) return PSLA_OK;
+    const size_t bytes = static_cast<size_t>(n_clips) * target_length * h->nmel * sizeof(float);
+    const char *a = reinterpret_cast<const char*>(in), *b = reinterpret_cast<const char*>(out);
+    if (a < b + bytes && b < a + bytes) return PSLA_E_INVALID;  // a roll cannot run in place
+    for (int i = 0; i < n_clips; ++i)
+        if (!(scale[i] == scale[i]) || shift[i] <= -target_length || shift[i] >= target_length) return PSLA_E_INVALID;
+    DeviceGuard guard(h->device);
+    if (!guard.ok) return PSLA_E_CUDA;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    const bool vec = h->nmel == 128 && (reinterpret_cast<size_t>(in) % 16 == 0) && (reinterpret_cast<size_t>(out) % 16 == 0) &&
+                     (!noise || reinterpret_cast<size_t>(noise) % 16 == 0);
+    for (int c0 = 0; c0 < n_clips; c0 += kNoiseClips) {
+        const int n = n_clips - c0 < kNoiseClips ? n_clips - c0 : kNoiseClips;
+        NoiseMeta meta;
+        for (int i = 0; i < n; ++i) {
+            meta.scale[i] = scale[c0 + i];
+            const int s = shift[c0 + i];
+            meta.shift[i] = s < 0 ? s + target_length : s;  // torch.roll: element t moves to (t + shift) mod T
+        }
+        const size_t off = static_cast<size_t>(c0) * target_length * h->nmel;
+        const long long rows = static_cast<long long>(n) * target_length;
+        const unsigned grid = static_cast<unsigned>((rows + 7) / 8);
+        if (vec) noise_roll_kernel<true><<<grid, 256, 0, stream>>>(in + off, out + off, noise ? noise + off : nullptr, meta, n, target_length, h->nmel, seed, c0);
+        else noise_roll_kernel<false><<<grid, 256, 0, stream>>>(in + off, out + off, noise ? noise + off : nullptr, meta, n, target_length, h->nmel, seed, c0);
+        PSLA_CUDA(h, cudaGetLastError());
+        h->launches += 1;
+    }
+    return PSLA_OK;
 }
 
 int psla_frontend_num_frames(const psla_frontend_t* h, int64_t n_samples) {

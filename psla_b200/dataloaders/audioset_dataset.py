@@ -75,6 +75,7 @@ class RawItem:
     wave2: Optional[torch.Tensor]  # partner waveform or None
     params: P.ItemParams
     labels: torch.Tensor  # [label_num] float32 (multi-hot, or mixup-soft)
+    noise: Optional[torch.Tensor] = None  # [T, F] U[0,1) field of the noise augmentation when it is drawn on the host
 
 
 @dataclass
@@ -85,6 +86,9 @@ class RawBatch:
     lam: np.ndarray
     masks: np.ndarray
     labels: torch.Tensor  # [B, C]
+    noise_scale: Optional[np.ndarray] = None  # [B] float64, set when the noise / roll augmentation is on
+    roll: Optional[np.ndarray] = None  # [B] int32
+    noise: Optional[torch.Tensor] = None  # [B, T, F] host-drawn fields (pinned), or None: the kernel draws them
 
     def __len__(self):
         return len(self.src1)
@@ -109,9 +113,13 @@ class AudiosetDataset(Dataset):
         self.norm_std = self.audio_conf.get("std")
         self.skip_norm = self.audio_conf.get("skip_norm") if self.audio_conf.get("skip_norm") else False
         self.noise = self.audio_conf.get("noise")
-        if self.noise == True:  # noqa: E712  (the reference compares with ==, :81)
-            raise NotImplementedError("noise/roll augmentation (audioset_dataset.py:197-199) is off in every "
-                                      "reference recipe (run.py:77) and not part of the GPU frontend yet")
+        # noise / roll augmentation (:197-199; off in every recipe, run.py:77,80).  The three draws always happen on the
+        # host in the reference's order, so the RNG streams stay aligned with the reference; `noise_field` (an extra
+        # key, not in the reference) says where the U[0,1) field comes from: "host" ships the drawn torch.rand(T, F)
+        # to the GPU (bit-exact), "device" drops it and lets the kernel draw its own (same distribution, no 540 KB per clip).
+        self.noise_field = self.audio_conf.get("noise_field", "host")
+        if self.noise_field not in ("host", "device"):
+            raise ValueError("audio_conf['noise_field'] must be 'host' or 'device'")
         self.index_dict = make_index_dict(label_csv)
         self.label_num = len(self.index_dict)
         say("number of classes is {:d}".format(self.label_num))
@@ -142,7 +150,14 @@ class AudiosetDataset(Dataset):
             for label_str in datum["labels"].split(","):
                 label_indices[int(self.index_dict[label_str])] = 1.0
         mask = P.draw_masks(self.freqm, self.timem, self.melbins, self.audio_conf.get("target_length"))
-        return RawItem(w1, w2, P.ItemParams(mixed, partner, lam, mask), torch.FloatTensor(label_indices))
+        params = P.ItemParams(mixed, partner, lam, mask)
+        field = None
+        if self.noise == True:  # noqa: E712  (the reference compares with ==, :197)
+            field, params.noise_scale, params.roll = P.draw_noise(self.audio_conf.get("target_length"), self.melbins, np.random)
+            if self.noise_field == "device":
+                field = None
+            params.noise = True
+        return RawItem(w1, w2, params, torch.FloatTensor(label_indices), field)
 
     # ---- batch assembly ----
     @staticmethod
@@ -164,8 +179,15 @@ class AudiosetDataset(Dataset):
             lam.append(it.params.lam)
             masks.append(it.params.mask)
         packed = pack_waveforms(waves, device=None, pinned=pinned)
-        return RawBatch(packed, np.array(src1, np.int32), np.array(src2, np.int32), np.array(lam, np.float64),
-                        np.array(masks, np.int32).reshape(-1, 4), torch.stack([it.labels for it in items]))
+        batch = RawBatch(packed, np.array(src1, np.int32), np.array(src2, np.int32), np.array(lam, np.float64),
+                         np.array(masks, np.int32).reshape(-1, 4), torch.stack([it.labels for it in items]))
+        if any(getattr(it.params, "noise", False) for it in items):
+            batch.noise_scale = np.array([it.params.noise_scale for it in items], np.float64)
+            batch.roll = np.array([it.params.roll for it in items], np.int32)
+            if all(it.noise is not None for it in items):
+                field = torch.stack([it.noise for it in items])
+                batch.noise = field.pin_memory() if pinned else field
+        return batch
 
 
 class FrontendLoader:
@@ -181,7 +203,11 @@ class FrontendLoader:
     def features(self, batch: RawBatch) -> torch.Tensor:
         dev = self.frontend.device
         waves = PackedWaves(batch.waves.wav.to(dev, non_blocking=True), batch.waves.offsets, batch.waves.lengths)
-        return self.frontend.forward_packed(waves, batch.src1, batch.src2, batch.lam, batch.masks)
+        fbank = self.frontend.forward_packed(waves, batch.src1, batch.src2, batch.lam, batch.masks)
+        if batch.noise_scale is not None:  # audioset_dataset.py:197-199, after the normalisation
+            self._noise_calls = getattr(self, "_noise_calls", 0) + 1
+            fbank = self.frontend.noise_roll(fbank, batch.noise_scale, batch.roll, batch.noise, seed=self._noise_calls)
+        return fbank
 
     def __iter__(self):
         for batch in self.loader:

@@ -233,6 +233,32 @@ class GpuFbankFrontend:
         _lib.check(st, "psla_frontend_forward", self._h)
         return out
 
+    def noise_roll(self, fbank: torch.Tensor, scale, roll, noise: Optional[torch.Tensor] = None, seed: int = 0,
+                   out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """The noise / roll augmentation of audioset_dataset.py:197-199 on a batch of features:
+        `roll(fbank[b] + noise[b] * scale[b] / 10, roll[b], dim=time)`.  `scale` / `roll`: the host's np.random.rand() /
+        np.random.randint(-10, 10) draws per clip.  `noise`: the torch.rand(T, F) fields the host drew ([B, T, F], moved to
+        the device here) for bit-exact parity, or None to let the kernel draw them (Philox, keyed by `seed`)."""
+        if not fbank.is_cuda or fbank.dtype != torch.float32 or not fbank.is_contiguous() or fbank.dim() != 3:
+            raise ValueError("fbank must be a contiguous float32 [B, T, F] cuda tensor")
+        B, T, F = fbank.shape
+        if F != self.num_mel_bins:
+            raise ValueError("feature width differs from num_mel_bins")
+        if out is None:
+            out = torch.empty_like(fbank)
+        if noise is not None:
+            noise = noise.to(self.device, dtype=torch.float32, non_blocking=True).contiguous()
+            if tuple(noise.shape) != (B, T, F):
+                raise ValueError("noise must be [B, T, F]")
+        asc = np.ascontiguousarray(np.asarray(scale, dtype=np.float64).astype(np.float32).reshape(B))
+        ash = np.ascontiguousarray(np.asarray(roll, dtype=np.int32).reshape(B))
+        st = self.lib.psla_frontend_noise_roll(
+            self._h, fbank.data_ptr(), out.data_ptr(), None if noise is None else noise.data_ptr(),
+            asc.ctypes.data_as(ctypes.POINTER(ctypes.c_float)), ash.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)),
+            B, T, int(seed) & (2**64 - 1), torch.cuda.current_stream(self.device).cuda_stream)
+        _lib.check(st, "psla_frontend_noise_roll", self._h)
+        return out
+
     def forward_host(self, packed: PackedWaves, src1, src2=None, lam=None, masks=None,
                      out_host: Optional[torch.Tensor] = None, target_length: Optional[int] = None,
                      stream: Optional[torch.cuda.Stream] = None) -> Optional[torch.Tensor]:

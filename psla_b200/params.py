@@ -6,6 +6,7 @@
   np.random.beta(10, 10)     mix lambda                         (:114)
   torch.rand(1) x2           frequency mask, only if freqm != 0 (:183 -> functional.py:939-940)
   torch.rand(1) x2           time mask, only if timem != 0      (:185)
+  torch.rand(T, F), np.random.rand(), np.random.randint(-10, 10)   noise field, its scale, roll -- only if noise (:197-199)
 The GPU kernels take the resulting integers / lambda as inputs, so with the same seeds the host
 reproduces the reference's augmentation decisions exactly.
 """
@@ -25,6 +26,9 @@ class ItemParams:
     partner: int  # dataset index of the partner, -1 if not mixed
     lam: float  # float64 lambda, 0.0 if not mixed (what _wav2fbank returns, :134-137)
     mask: Tuple[int, int, int, int]  # f_start, f_width, t_start, t_width (width 0 = no mask)
+    noise_scale: float = 0.0  # np.random.rand() of :198 (0.0 when the noise augmentation is off)
+    roll: int = 0  # np.random.randint(-10, 10) of :199
+    noise: bool = False  # the noise / roll augmentation applies to this item
 
 
 def axis_mask(mask_param: int, axis_size: int) -> Tuple[int, int]:
@@ -52,3 +56,12 @@ def draw_mixup(mixup: float, n_items: int, py_random=_py_random) -> Tuple[bool, 
 
 def draw_lambda(np_random=np.random) -> float:
     return float(np_random.beta(10, 10))
+
+
+def draw_noise(target_length: int, num_mel_bins: int, np_random=np.random) -> Tuple[torch.Tensor, float, int]:
+    """The three draws of the noise / roll augmentation in the reference's order (:198-199): the U[0,1) field from
+    torch's generator, then the scale and the roll from numpy's."""
+    field = torch.rand(target_length, num_mel_bins)
+    scale = float(np_random.rand())
+    roll = int(np_random.randint(-10, 10))
+    return field, scale, roll

@@ -125,12 +125,35 @@ def test_pack_waveforms_alignment_and_content():
     assert torch.equal(p.wav[16:19], ws[2])
 
 
-def test_noise_flag_is_rejected_not_silently_ignored():
+def test_noise_draws_keep_the_reference_rng_order(golden_dir):
+    """noise == True (audioset_dataset.py:197-199): three more draws per item (torch.rand(T, F), np.random.rand(),
+    np.random.randint(-10, 10)).  numpy's generator also feeds the mixup lambdas, so bit-identical soft labels over two
+    passes prove the draws are consumed in the reference's order; the fields are kept ("host") or dropped ("device")."""
+    g = np.load(os.path.join(golden_dir, "getitem_noise.npz"))
+    conf = json.loads(str(g["conf"]))
     with tempfile.TemporaryDirectory() as tmp:
-        conf = {"num_mel_bins": 128, "target_length": 96, "freqm": 0, "timem": 0, "mixup": 0, "dataset": "audioset",
-                "mode": "train", "mean": 0.0, "std": 1.0, "noise": True}
-        with pytest.raises(NotImplementedError):
-            _tiny_dataset(tmp, conf)
+        ds, waves = _tiny_dataset(tmp, conf)
+        k = 0
+        items = []
+        for seed in g["seeds"]:
+            random.seed(int(seed)); np.random.seed(int(seed)); torch.manual_seed(int(seed))
+            for i in range(len(ds)):
+                it = ds[i]
+                assert np.array_equal(it.labels.numpy(), g["labels"][k]), k
+                assert it.params.noise and 0.0 <= it.params.noise_scale < 1.0 and -10 <= it.params.roll < 10
+                assert it.noise.shape == (96, 128) and 0.0 <= float(it.noise.min()) and float(it.noise.max()) < 1.0
+                items.append(it)
+                k += 1
+        batch = ds.collate(items[:4], pinned=False)
+        assert batch.noise.shape == (4, 96, 128) and batch.noise_scale.shape == (4,) and batch.roll.dtype == np.int32
+        ds2, _ = _tiny_dataset(tmp, {**conf, "noise_field": "device"})
+        random.seed(0); np.random.seed(0); torch.manual_seed(0)
+        it2 = [ds2[i] for i in range(len(ds2))]
+        assert all(a.noise is None for a in it2)
+        assert [a.params.roll for a in it2] == [a.params.roll for a in items[:len(it2)]]  # same streams either way
+        assert ds2.collate(it2, pinned=False).noise is None
+        with pytest.raises(ValueError):
+            _tiny_dataset(tmp, {**conf, "noise_field": "gpu"})
 
 
 def test_frontend_needs_cuda():

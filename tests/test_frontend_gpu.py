@@ -418,3 +418,58 @@ def test_c4_long_recording_chunks_equal_per_clip_oracle(FE):
     starts, y = lr.predict(lambda f: f.mean(dim=(1, 2)).unsqueeze(1), batch=4)
     assert y.shape == (7, 1) and starts.tolist() == lr.starts.tolist()
     fe.close()
+
+
+def test_noise_roll_augmentation_matches_reference_getitem(FE, golden_dir):
+    """audioset_dataset.py:197-199 through the drop-in dataset + loader: with the host-drawn U[0,1) fields the output
+    equals the unmodified reference's __getitem__ (same seeds); with device-drawn fields only the distribution can."""
+    from psla_b200.dataloaders import AudiosetDataset, FrontendLoader
+    g = np.load(os.path.join(golden_dir, "getitem_noise.npz"))
+    conf = json.loads(str(g["conf"]))
+    waves = tiny_dataset_waves()
+    store = {f"mem://{i}.wav": w for i, w in enumerate(waves)}
+    with tempfile.TemporaryDirectory() as tmp:
+        jpath, cpath = os.path.join(tmp, "t.json"), os.path.join(tmp, "l.csv")
+        json.dump({"data": [{"wav": f"mem://{i}.wav", "labels": TINY_LABELS[i]} for i in range(len(waves))]}, open(jpath, "w"))
+        with open(cpath, "w") as f:
+            f.write("index,mid,display_name\n" + "".join(f"{i},{m},c{i}\n" for i, m in enumerate(TINY_CLASSES)))
+        load = lambda p: (store[p].clone(), 16000)  # noqa: E731
+        fe = FE(conf)
+        outs = {}
+        for mode in ("host", "device"):
+            ds = AudiosetDataset(jpath, {**conf, "noise_field": mode}, cpath, loader=load, verbose=False)
+            items = []
+            for seed in g["seeds"]:
+                random.seed(int(seed)); np.random.seed(int(seed)); torch.manual_seed(int(seed))
+                items += [ds[i] for i in range(len(ds))]
+            batch = ds.collate(items)
+            outs[mode] = (FrontendLoader(None, fe).features(batch).cpu(), batch)
+        feats, batch = outs["host"]
+        ref = torch.from_numpy(g["feats"])
+        assert ((feats - ref).abs() * conf["std"]).max().item() <= TOL
+        assert torch.equal(batch.labels, torch.from_numpy(g["labels"]))
+        # the kernel alone against torch ops on the same inputs: bit-exact (same two roundings per cell, exact row moves)
+        base = fe.forward_packed(PackedWavesOf(batch, fe.device), batch.src1, batch.src2, batch.lam, batch.masks)
+        want = torch.stack([torch.roll(base[b].cpu() + batch.noise[b] * float(np.float32(batch.noise_scale[b])) / 10, int(batch.roll[b]), 0)
+                            for b in range(len(batch))])
+        assert torch.equal(feats, want)
+        # device-drawn fields: undo the roll, subtract the clean features -> U[0, scale / 10) per clip
+        dfeats, dbatch = outs["device"]
+        assert np.array_equal(dbatch.roll, batch.roll) and dbatch.noise is None
+        for b in range(len(dbatch)):
+            u = (torch.roll(dfeats[b], -int(dbatch.roll[b]), 0) - base[b].cpu()) * 10 / max(float(dbatch.noise_scale[b]), 1e-3)
+            if dbatch.noise_scale[b] > 0.05:
+                assert -1e-3 <= u.min().item() and u.max().item() <= 1.0 + 1e-3
+                assert abs(u.mean().item() - 0.5) < 0.02 and abs(u.std().item() - 0.2887) < 0.02
+        assert not torch.equal(dfeats[0], dfeats[len(waves)])  # different clips, different fields
+        # argument checks of the C entry point
+        with pytest.raises(Exception):
+            fe.noise_roll(base, batch.noise_scale, batch.roll, out=base)  # in place
+        with pytest.raises(Exception):
+            fe.noise_roll(base, batch.noise_scale, np.full(len(batch), 96, np.int32))  # |shift| >= T
+        fe.close()
+
+
+def PackedWavesOf(batch, device):
+    from psla_b200.frontend import PackedWaves
+    return PackedWaves(batch.waves.wav.to(device), batch.waves.offsets, batch.waves.lengths)

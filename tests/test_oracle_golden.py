@@ -115,3 +115,27 @@ def test_short_clip_raises():
     assert O.kaldi_fbank_np(np.zeros(400, np.float32), dtype=np.float32).shape == (1, 128)
     z = O.kaldi_fbank_np(np.zeros(1000, np.float32), dtype=np.float32)
     assert np.allclose(z, np.log(np.float32(O.EPS32)))
+
+
+@pytest.mark.parametrize("use_torchaudio", [True, False])
+def test_getitem_restatement_with_noise_and_roll(golden_dir, use_torchaudio):
+    """audioset_dataset.py:197-199 (noise == True): every cell carries noise, so there is no fill pattern to compare;
+    the values must agree with the unmodified reference's output under the same seeds (same three extra draws)."""
+    g = _load(golden_dir, "getitem_noise.npz")
+    conf = json.loads(str(g["conf"]))
+    assert conf["noise"] is True
+    waves = tiny_dataset_waves()
+    k = 0
+    for seed in g["seeds"]:
+        random.seed(int(seed))
+        np.random.seed(int(seed))
+        torch.manual_seed(int(seed))
+        for i in range(len(waves)):
+            out, _ = O.item_torch(waves, i, conf, random, np.random, use_torchaudio=use_torchaudio)
+            assert np.abs(out.numpy() - g["feats"][k]).max() <= HOST_DRIFT, k
+            k += 1
+    assert k == len(g["feats"])
+    # the explicit form: roll by s moves row t to (t + s) mod T, noise is added before the roll
+    fb, field = torch.arange(12.0).reshape(6, 2), torch.ones(6, 2)
+    y = O.noise_roll_torch(fb, field, 0.5, -2)
+    assert torch.allclose(y[4], fb[0] + 0.05) and torch.allclose(y[0], fb[2] + 0.05)

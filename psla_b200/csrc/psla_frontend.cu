@@ -130,26 +130,35 @@ int probe_lg2_eps(psla_frontend* h) {
     return PSLA_OK;
 }
 
-template <bool EXACT, bool MELSPEC, bool PMETA, class S>
+template <bool EXACT, bool MELSPEC, bool PMETA, class S, bool TRACE>
 cudaError_t prepare_one(size_t smem) {
-    cudaError_t e = cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC, PMETA, S>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC, PMETA, S, TRACE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(smem));
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC, PMETA, S>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    return cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC, PMETA, S, TRACE>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
 }
-template <bool EXACT, bool MELSPEC>
+template <bool EXACT, bool MELSPEC, bool TRACE>
 cudaError_t prepare_kernel(size_t smem) {
-    cudaError_t e = prepare_one<EXACT, MELSPEC, false, float>(smem);
-    if (e == cudaSuccess) e = prepare_one<EXACT, MELSPEC, true, float>(smem);
-    if (e == cudaSuccess) e = prepare_one<EXACT, MELSPEC, false, short>(smem);
-    if (e == cudaSuccess) e = prepare_one<EXACT, MELSPEC, true, short>(smem);
+    cudaError_t e = prepare_one<EXACT, MELSPEC, false, float, TRACE>(smem);
+    if (e == cudaSuccess) e = prepare_one<EXACT, MELSPEC, true, float, TRACE>(smem);
+    if (e == cudaSuccess) e = prepare_one<EXACT, MELSPEC, false, short, TRACE>(smem);
+    if (e == cudaSuccess) e = prepare_one<EXACT, MELSPEC, true, short, TRACE>(smem);
     return e;
 }
 
-// launch of the variant selected at run time
+// launch of the variant selected at run time (the tracing variants exist for the default clip-mean mode only)
 template <class S>
-cudaError_t launch_stream_kernel(const cudaLaunchConfig_t& cfg, bool exact, bool spec, bool pmeta, const StreamParams& p, const MetaBlock& mb) {
+cudaError_t launch_stream_kernel(const cudaLaunchConfig_t& cfg, bool exact, bool spec, bool pmeta, bool trace, const StreamParams& p,
+                                 const MetaBlock& mb) {
     const MetaNone none = {0};
+    if (trace) {
+        switch ((spec ? 2 : 0) | (pmeta ? 1 : 0)) {
+            case 0: return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, false, false, S, true>, p, none);
+            case 1: return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, false, true, S, true>, p, mb);
+            case 2: return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, true, false, S, true>, p, none);
+            default: return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, true, true, S, true>, p, mb);
+        }
+    }
     switch ((exact ? 4 : 0) | (spec ? 2 : 0) | (pmeta ? 1 : 0)) {
         case 0: return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, false, false, S>, p, none);
         case 1: return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, false, true, S>, p, mb);
@@ -179,10 +188,12 @@ int upload_tables(psla_frontend* h) {
     h->tab_floats = total;
     h->smem_bytes = smem;
     h->mel_spec = spec;
-    PSLA_CUDA(h, (prepare_kernel<false, false>(smem)));
-    PSLA_CUDA(h, (prepare_kernel<false, true>(smem)));
-    PSLA_CUDA(h, (prepare_kernel<true, false>(smem)));
-    PSLA_CUDA(h, (prepare_kernel<true, true>(smem)));
+    PSLA_CUDA(h, (prepare_kernel<false, false, false>(smem)));
+    PSLA_CUDA(h, (prepare_kernel<false, true, false>(smem)));
+    PSLA_CUDA(h, (prepare_kernel<true, false, false>(smem)));
+    PSLA_CUDA(h, (prepare_kernel<true, true, false>(smem)));
+    PSLA_CUDA(h, (prepare_kernel<false, false, true>(smem)));
+    PSLA_CUDA(h, (prepare_kernel<false, true, true>(smem)));
     PSLA_CUDA(h, cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, h->device));
     return PSLA_OK;
 }
@@ -665,8 +676,10 @@ int forward_any(psla_frontend_t* h, const void* wav, bool pcm16, const int64_t* 
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = overlap_ok ? 1 : 0;
-    const cudaError_t le = pcm16 ? launch_stream_kernel<short>(cfg, h->exact_mean, h->mel_spec, param_meta, p, h->meta_host)
-                                 : launch_stream_kernel<float>(cfg, h->exact_mean, h->mel_spec, param_meta, p, h->meta_host);
+    const bool trace = h->trace != nullptr;
+    if (trace && h->exact_mean) return PSLA_E_UNSUPPORTED;  // the timeline is compiled for the default clip-mean mode only
+    const cudaError_t le = pcm16 ? launch_stream_kernel<short>(cfg, h->exact_mean, h->mel_spec, param_meta, trace, p, h->meta_host)
+                                 : launch_stream_kernel<float>(cfg, h->exact_mean, h->mel_spec, param_meta, trace, p, h->meta_host);
     PSLA_CUDA(h, le);
     PSLA_CUDA(h, cudaGetLastError());
     if (slot) {

@@ -730,7 +730,7 @@ constexpr int kStageIters = StageGeom<kOverlapSamples, kGroupSamples>::kIters;  
 // one live group whose window is staged: frame means, pass 1, (shift), pass 2, power, (prefetch), mel, epilogue.
 // Everything it needs beyond the kernel parameters comes from the warp's shared-memory state (CS_*).  The prefetch
 // leaves the next group's 640 new samples in ra / rc; the caller commits them at the top of its next step.
-template <bool MELSPEC, class S>
+template <bool MELSPEC, class S, bool TRACE>
 __device__ __forceinline__ void process_group(const StreamParams& p, const float* TAB, float* WS, int lane,
                                               typename Pcm<S>::reg_t (&ra)[kStageIters], typename Pcm<S>::reg_t (&rc)[kStageIters]) {
     float* D = WS + kWsD;
@@ -764,7 +764,7 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
         pair_pass1_store(n2, TAB + kTabTwz, EX + h * kExSecondPair, z);
     }
     __syncwarp();
-    if (p.trace) trace_phase(p, cs, lane, 6);
+    if (TRACE && p.trace) trace_phase(p, cs, lane, 6);
     {
         // pass 2 re-maps the lanes: pair h2 = lane & 1, row t = lane >> 1 (see kExSecondPair)
         const int h2 = lane & 1, t = lane >> 1;
@@ -774,7 +774,7 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
         pair_power_store(t, h2, za, zb, EX);
     }
     __syncwarp();
-    if (p.trace) trace_phase(p, cs, lane, 7);
+    if (TRACE && p.trace) trace_phase(p, cs, lane, 7);
     {
         const int4 ls = cs_q(cs, CS_B);  // b, g, budget, next
         if (ls.w & kNextLive) {  // prefetch the next group's 640 new samples; they are consumed after the epilogue
@@ -782,7 +782,7 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
             const int S1 = (ls.y + 1) * kStepSamples;
             if (ls.w & kNextFull) stage_issue<kOverlapSamples, kGroupSamples, true>(m, S1, lane, ra, rc);
             else stage_issue<kOverlapSamples, kGroupSamples, false>(m, S1, lane, ra, rc);
-            if (p.trace) trace_phase(p, cs, lane, 11);
+            if (TRACE && p.trace) trace_phase(p, cs, lane, 11);
         }
     }
     float acc[kMelSlots][kGroupFrames];
@@ -794,7 +794,7 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
         mt.w = TAB + kTabMelW;
         warp_mel<MELSPEC>(lane, EX, mt, acc);
     }
-    if (p.trace) trace_phase(p, cs, lane, 8);
+    if (TRACE && p.trace) trace_phase(p, cs, lane, 8);
     {
         const int4 l2 = cs_q(cs, CS_B);
         const int f0 = l2.y * kGroupFrames;
@@ -804,14 +804,15 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
         if (p.fast_log) epilogue<true, MELSPEC ? kMaxMel : 0>(p, cs, mel_bin, lane, f0, out, acc);
         else epilogue<false, MELSPEC ? kMaxMel : 0>(p, cs, mel_bin, lane, f0, out, acc);
     }
-    if (p.trace) trace_phase(p, cs, lane, 9);
+    if (TRACE && p.trace) trace_phase(p, cs, lane, 9);
 }
 
 // ------------------------------------------------------------------------------------------------
 // Kernel 2: the streaming kernel.  grid = two CTAs per SM, block = 8 warps, no CTA barrier after the table load.
 // Warp r of W owns the groups whose preceding cost lies in [r*C/W, (r+1)*C/W)  (clip-major order).
 // ------------------------------------------------------------------------------------------------
-template <bool EXACT, bool MELSPEC, bool PMETA, class S>
+// TRACE: the per-warp timeline (StreamParams::trace) is compiled in; the production variants carry none of its checks
+template <bool EXACT, bool MELSPEC, bool PMETA, class S, bool TRACE = false>
 __global__ void __launch_bounds__(kThreads, 2)
     fbank_stream_kernel(const __grid_constant__ StreamParams p, const __grid_constant__ std::conditional_t<PMETA, MetaBlock, MetaNone> meta) {
     using MS = std::conditional_t<PMETA, ParamMeta, GlobalMeta>;
@@ -834,7 +835,7 @@ __global__ void __launch_bounds__(kThreads, 2)
     const float4* tsrc = reinterpret_cast<const float4*>(p.tab);
     float4 tv = make_float4(0.f, 0.f, 0.f, 0.f);
     if (tid < n4) tv = __ldg(tsrc + tid);
-    if (p.trace) trace_begin(cs, lane);
+    if (TRACE && p.trace) trace_begin(cs, lane);
     // this warp's share of the work
     const long long W = static_cast<long long>(gridDim.x) * kWarpsPerCta;
     const long long r = static_cast<long long>(warp) * gridDim.x + blockIdx.x;  // neighbouring ranges on different SMs
@@ -853,13 +854,13 @@ __global__ void __launch_bounds__(kThreads, 2)
     }
     __syncthreads();
     if (!has_work) {
-        if (p.trace) trace_end(p, cs, lane);
+        if (TRACE && p.trace) trace_end(p, cs, lane);
         return;
     }
     int loaded_b = -1;
     bool staged = false;  // the current group's overlap samples are in the window and its new samples in ra / rc
     typename Pcm<S>::reg_t ra[kStageIters], rc[kStageIters];
-    if (p.trace) trace_mark(cs, lane);
+    if (TRACE && p.trace) trace_mark(cs, lane);
 
     while (true) {
         const int4 ls = cs_q(cs, CS_B);
@@ -870,14 +871,14 @@ __global__ void __launch_bounds__(kThreads, 2)
             enter_clip<EXACT>(p, ms, b, lane, cs);
             loaded_b = b;
             staged = false;
-            if (p.trace) trace_phase(p, cs, lane, 4);
+            if (TRACE && p.trace) trace_phase(p, cs, lane, 4);
         }
         const int4 dq = cs_q(cs, CS_MEFF);  // m_eff, a_lo, a_hi, b_lo
         if (is_dead(dq.y, dq.z, dq.w, g)) {
             // a run of constant rows: take as many of its groups as the budget covers, one contiguous fill
             const int run_end = (g >= dq.w) ? p.G : dq.z;
             const int n = min(run_end - g, (budget + p.cm.dead - 1) / p.cm.dead);
-            if (p.trace) trace_count(p, cs, lane, CS_TR_DEAD, n);
+            if (TRACE && p.trace) trace_count(p, cs, lane, CS_TR_DEAD, n);
             const int row0 = kGroupFrames * g, row1 = min(p.T, kGroupFrames * (g + n));
             warp_fill(p.out + (static_cast<size_t>(b) * p.T + row0) * p.nmel, static_cast<long long>(row1 - row0) * p.nmel, p.fill, lane);
             const bool wrap = g + n == p.G;
@@ -886,7 +887,7 @@ __global__ void __launch_bounds__(kThreads, 2)
             __syncwarp();
             continue;
         }
-        if (p.trace) trace_count(p, cs, lane, staged ? CS_TR_LIVE : CS_TR_COLD, 1);
+        if (TRACE && p.trace) trace_count(p, cs, lane, staged ? CS_TR_LIVE : CS_TR_COLD, 1);
         bool next_live;
         {
             MixState<S> m = load_mix<S>(cs, p.wav);
@@ -911,7 +912,7 @@ __global__ void __launch_bounds__(kThreads, 2)
                     stage_issue<0, kOverlapSamples, false>(m, S0, lane, ha, hc);
                     stage_issue<kOverlapSamples, kGroupSamples, false>(m, S0, lane, ra, rc);
                 }
-                if (p.trace) trace_phase(p, cs, lane, 10);
+                if (TRACE && p.trace) trace_phase(p, cs, lane, 10);
                 if (!EXACT) {
                     m.sub1 = m.mix ? fmaf(m.l1, a0, m.l2 * c0) : a0;
                     cs_set(cs, CS_SUB1, __float_as_int(m.sub1), lane);
@@ -924,7 +925,7 @@ __global__ void __launch_bounds__(kThreads, 2)
             }
             if (full) stage_commit<EXACT, kOverlapSamples, kGroupSamples, true>(m, S0, lane, p.preemph, p.c1, ra, rc, D, BS, XS, carry);
             else stage_commit<EXACT, kOverlapSamples, kGroupSamples, false>(m, S0, lane, p.preemph, p.c1, ra, rc, D, BS, XS, carry);
-            if (p.trace) trace_phase(p, cs, lane, 5);
+            if (TRACE && p.trace) trace_phase(p, cs, lane, 5);
             budget -= p.cm.live + (run_start(dq.y, dq.z, g) ? p.cm.cold : 0);
             next_live = (g + 1 < p.G) && !is_dead(dq.y, dq.z, dq.w, g + 1) && budget > 0;
             const bool full_next = next_live && window_full(m, (g + 1) * kStepSamples);
@@ -934,7 +935,7 @@ __global__ void __launch_bounds__(kThreads, 2)
             }
         }
         __syncwarp();
-        process_group<MELSPEC, S>(p, TAB, WS, lane, ra, rc);
+        process_group<MELSPEC, S, TRACE>(p, TAB, WS, lane, ra, rc);
         staged = next_live;
         {  // advance (CS_B / CS_G are read by process_group, so they move only now)
             const int4 l2 = cs_q(cs, CS_B);
@@ -943,7 +944,7 @@ __global__ void __launch_bounds__(kThreads, 2)
         }
         __syncwarp();
     }
-    if (p.trace) trace_end(p, cs, lane);
+    if (TRACE && p.trace) trace_end(p, cs, lane);
 }
 
 }  // namespace psla

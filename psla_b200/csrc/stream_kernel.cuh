@@ -731,7 +731,7 @@ constexpr int kStageIters = StageGeom<kOverlapSamples, kGroupSamples>::kIters;  
 // Everything it needs beyond the kernel parameters comes from the warp's shared-memory state (CS_*).  The prefetch
 // leaves the next group's 640 new samples in ra / rc; the caller commits them at the top of its next step.
 template <bool MELSPEC, class S, bool TRACE>
-__device__ __forceinline__ void process_group(const StreamParams& p, const float* TAB, float* WS, int lane,
+__device__ __forceinline__ void process_group(const StreamParams& p, const float* TAB, float* WS, int lane, const int b, const int gn,
                                               typename Pcm<S>::reg_t (&ra)[kStageIters], typename Pcm<S>::reg_t (&rc)[kStageIters]) {
     float* D = WS + kWsD;
     float* BS = WS + kWsBS;
@@ -757,7 +757,7 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
         cf z[32];
         pair_pass1(n2, h, D, XS, TAB + kTabWin, cmu_x, cmu_y, z);
         __syncwarp();  // EX aliases D: every lane has its samples in registers ...
-        if (cs_i(cs, CS_NEXT) & kNextLive) {
+        if (gn & kNextLive) {
             stage_shift(lane, D, BS, XS);  // ... and the part the next group shares has moved below kWsEX
             __syncwarp();
         }
@@ -776,11 +776,10 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
     __syncwarp();
     if (TRACE && p.trace) trace_phase(p, cs, lane, 7);
     {
-        const int4 ls = cs_q(cs, CS_B);  // b, g, budget, next
-        if (ls.w & kNextLive) {  // prefetch the next group's 640 new samples; they are consumed after the epilogue
+        if (gn & kNextLive) {  // prefetch the next group's 640 new samples; they are consumed after the epilogue
             const MixState<S> m = load_mix<S>(cs, p.wav);
-            const int S1 = (ls.y + 1) * kStepSamples;
-            if (ls.w & kNextFull) stage_issue<kOverlapSamples, kGroupSamples, true>(m, S1, lane, ra, rc);
+            const int S1 = ((gn >> 2) + 1) * kStepSamples;
+            if (gn & kNextFull) stage_issue<kOverlapSamples, kGroupSamples, true>(m, S1, lane, ra, rc);
             else stage_issue<kOverlapSamples, kGroupSamples, false>(m, S1, lane, ra, rc);
             if (TRACE && p.trace) trace_phase(p, cs, lane, 11);
         }
@@ -796,9 +795,8 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
     }
     if (TRACE && p.trace) trace_phase(p, cs, lane, 8);
     {
-        const int4 l2 = cs_q(cs, CS_B);
-        const int f0 = l2.y * kGroupFrames;
-        float* out = p.out + static_cast<size_t>(l2.x) * p.T * p.nmel;
+        const int f0 = (gn >> 2) * kGroupFrames;
+        float* out = p.out + static_cast<size_t>(b) * p.T * p.nmel;
         const int* mel_bin = reinterpret_cast<const int*>(TAB + kTabMelBin);
         // MELSPEC is only selected for 128 mel bins: every (slot, lane) then owns a column
         if (p.fast_log) epilogue<true, MELSPEC ? kMaxMel : 0>(p, cs, mel_bin, lane, f0, out, acc);
@@ -862,10 +860,16 @@ __global__ void __launch_bounds__(kThreads, 2)
     typename Pcm<S>::reg_t ra[kStageIters], rc[kStageIters];
     if (TRACE && p.trace) trace_mark(cs, lane);
 
-    while (true) {
+    // loop state: clip, group and remaining budget stay in registers (three words live across the FFT phases); everything
+    // per clip lives in the warp's shared-memory words (CS_*)
+    int b, g, budget;
+    {
         const int4 ls = cs_q(cs, CS_B);
-        const int b = ls.x, g = ls.y;
-        int budget = ls.z;
+        b = ls.x;
+        g = ls.y;
+        budget = ls.z;
+    }
+    while (true) {
         if (b >= p.n_clips || budget <= 0) break;
         if (b != loaded_b) {
             enter_clip<EXACT>(p, ms, b, lane, cs);
@@ -882,13 +886,15 @@ __global__ void __launch_bounds__(kThreads, 2)
             const int row0 = kGroupFrames * g, row1 = min(p.T, kGroupFrames * (g + n));
             warp_fill(p.out + (static_cast<size_t>(b) * p.T + row0) * p.nmel, static_cast<long long>(row1 - row0) * p.nmel, p.fill, lane);
             const bool wrap = g + n == p.G;
-            if (lane == 0) cs_set_q(cs, CS_B, wrap ? b + 1 : b, wrap ? 0 : g + n, budget - n * p.cm.dead, 0);
+            budget -= n * p.cm.dead;
+            b = wrap ? b + 1 : b;
+            g = wrap ? 0 : g + n;
             staged = false;
-            __syncwarp();
             continue;
         }
         if (TRACE && p.trace) trace_count(p, cs, lane, staged ? CS_TR_LIVE : CS_TR_COLD, 1);
         bool next_live;
+        int gn;
         {
             MixState<S> m = load_mix<S>(cs, p.wav);
             const int S0 = g * kStepSamples;
@@ -929,18 +935,16 @@ __global__ void __launch_bounds__(kThreads, 2)
             budget -= p.cm.live + (run_start(dq.y, dq.z, g) ? p.cm.cold : 0);
             next_live = (g + 1 < p.G) && !is_dead(dq.y, dq.z, dq.w, g + 1) && budget > 0;
             const bool full_next = next_live && window_full(m, (g + 1) * kStepSamples);
-            if (lane == 0) {
-                cs_set_q(cs, CS_B, b, g, budget, (next_live ? kNextLive : 0) | (full_next ? kNextFull : 0));
-                cs[CS_CARRY] = __float_as_int(carry);
-            }
+            gn = (g << 2) | (next_live ? kNextLive : 0) | (full_next ? kNextFull : 0);
+            if (lane == 0) cs[CS_CARRY] = __float_as_int(carry);
         }
         __syncwarp();
-        process_group<MELSPEC, S, TRACE>(p, TAB, WS, lane, ra, rc);
+        process_group<MELSPEC, S, TRACE>(p, TAB, WS, lane, b, gn, ra, rc);
         staged = next_live;
-        {  // advance (CS_B / CS_G are read by process_group, so they move only now)
-            const int4 l2 = cs_q(cs, CS_B);
-            const bool wrap = l2.y + 1 == p.G;
-            if (lane == 0) cs_set_q(cs, CS_B, wrap ? l2.x + 1 : l2.x, wrap ? 0 : l2.y + 1, l2.z, 0);
+        {  // advance
+            const bool wrap = g + 1 == p.G;
+            b = wrap ? b + 1 : b;
+            g = wrap ? 0 : g + 1;
         }
         __syncwarp();
     }

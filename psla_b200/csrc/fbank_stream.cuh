@@ -14,7 +14,7 @@
 //            starts 160 samples = 10 n1-steps after the x frame, so ONE run of 35 staged values feeds both.
 //            -> 32-point DIT FFT over n1 in registers (FMA-only butterflies, first stage pruned for the 7 zero inputs) -> shared memory
 //            EX[k1][n2], untwiddled (row 0 pre-multiplied by W_32^-n2, see below).  EX aliases the staged samples (kWsEX).
-//   pass 2   lane t reads rows ka = t and kb = 32 - t (lane 0: rows 0 and 16), multiplies row ka by
+//   pass 2   lane t reads rows ka = t and kb = 32 - t (lane 0: rows 0 and 16; pass 1 stored them side by side), multiplies row ka by
 //            TW[t][n2] = W_512^(t*n2) and row kb by conj(TW[t][n2]): because W_512^((32-t)*n2) = W_16^n2 * conj(TW[t][n2])
 //            and a modulation by W_16^n2 only rotates the 16-point FFT's output index by one, both rows share one
 //            table row.  Two 16-point DIT FFTs over n2 in registers.  Z[k] and Z[512-k] are then in the SAME lane, so
@@ -36,6 +36,16 @@ PSLA_HD void st2(float* p, float a, float b) {
 #else
     p[0] = a;
     p[1] = b;
+#endif
+}
+PSLA_HD void st4(float* p, float a, float b, float c, float d) {
+#if defined(__CUDA_ARCH__)
+    *reinterpret_cast<float4*>(p) = make_float4(a, b, c, d);
+#else
+    p[0] = a;
+    p[1] = b;
+    p[2] = c;
+    p[3] = d;
 #endif
 }
 PSLA_HD void ld2(const float* p, float& a, float& b) {
@@ -80,14 +90,16 @@ PSLA_HDC int dpad(int u) { return u + 16 * (u / 320); }
 constexpr int kDFloats = 912;  // dpad(879) + 1
 constexpr int kBsFloats = 56;  // 55 sums of 16 samples
 constexpr int kXsFloats = 8;   // (1-p) * x at u = 0, 160, ..., 800
-// Exchange buffer of one frame pair: 32 rows (k1) x 16 complex (n2), row stride 36 floats so that pass-2 row reads
-// (LDS.128, one row per lane) are bank-conflict free.
-constexpr int kExRowFloats = 36;
-constexpr int kExPairFloats = 32 * kExRowFloats;  // 1152 floats = 4608 B
+// Exchange buffer of one frame pair, organised by the ROW PAIRS pass 2 consumes: EX[t][n2] = (Z1[ka][n2], Z1[kb][n2]) with
+// ka = t, kb = 32 - t (t = 0: rows 0 and 16) -- 16 bytes per (t, n2), so pass 1 stores and pass 2 loads are all 128-bit.
+// Row stride 68 floats: the 8 lanes of a quarter-warp (4 consecutive t x 2 pairs) read 8 distinct 16-byte bank groups.
+constexpr int kExRowFloats = 68;
+constexpr int kExPairFloats = 16 * kExRowFloats;  // 1088 floats = 4352 B
+constexpr int kTwRowFloats = 36;                  // row stride of the inter-pass twiddle table TW[t][n2]
 // Pass 2 interleaves the two pairs over the lanes (lane = 2 t + h, so that a lane pair stores the 4 frames of a bin as
 // one contiguous 16 bytes); the second pair's buffer starts 16 floats later so that (t, 0) and (t, 1) hit different banks.
 constexpr int kExSecondPair = kExPairFloats + 16;
-constexpr int kExFloats = kExSecondPair + kExPairFloats;  // 2320
+constexpr int kExFloats = kExSecondPair + kExPairFloats;  // 2192
 // Power spectra of the warp's 4 frames, P[bin][frame], alias the exchange buffers once pass 2 has read them.
 constexpr int kPFloats = 4 * (kNfft / 2);  // bins 0..255 (bin 256 never carries mel weight: kaldi.py:627 pads a zero column)
 static_assert(kPFloats <= kExFloats, "P must fit in the warp's exchange buffers");
@@ -111,7 +123,7 @@ static_assert((kWsEX * 4) % 16 == 0 && (kWsCS * 4) % 16 == 0 && (kWarpFloats * 4
 constexpr int kWinRow = 28;                            // WINT[n2][n1], n1 < 25, zero padded: 0.5 * window[16*n1 + n2]
 constexpr int kTabWin = 0;                             // [16][28]
 constexpr int kTabTw = kTabWin + 16 * kWinRow;         // [16][36]: TW[t][n2] (re, im), row stride 36 floats
-constexpr int kTabTwz = kTabTw + 16 * kExRowFloats;    // [16] (re, im): W_32^(-n2), applied to row 0 in pass 1
+constexpr int kTabTwz = kTabTw + 16 * kTwRowFloats;    // [16] (re, im): W_32^(-n2), applied to row 0 in pass 1
 constexpr int kTabMelStart = kTabTwz + 32;             // [4][32] ints: first P bin of (slot, lane)
 constexpr int kTabMelBin = kTabMelStart + 128;         // [4][32] ints: mel bin owned by (slot, lane), -1 = none
 constexpr int kTabMelInfo = kTabMelBin + 128;          // [8] ints: slot_max[4], slot_off[4] (rows of W before the slot)
@@ -162,12 +174,13 @@ PSLA_HD void pair_pass1(int n2, int h, const float* __restrict__ D, const float*
 PSLA_HD void pair_pass1_store(int n2, const float* __restrict__ TWZ, float* __restrict__ EX, const cf (&z)[32]) {
     float zr, zi;
     ld2(TWZ + 2 * n2, zr, zi);
-    static_for<0, 32>([&](auto r_) {
-        constexpr int r = decltype(r_)::value;
-        constexpr int k1 = brev<5>(r);
-        cf a = z[r];
-        if constexpr (k1 == 0) a = cmul(a, zr, zi);  // row 0 is read by lane 0 of pass 2, whose table row is W_32^n2: compensate
-        st2(EX + k1 * kExRowFloats + 2 * n2, a.x, a.y);
+    static_for<0, 16>([&](auto t_) {
+        constexpr int t = decltype(t_)::value;
+        constexpr int ka = t, kb = (t != 0) ? 32 - t : 16;
+        cf a = z[brev<5>(ka)];
+        const cf b = z[brev<5>(kb)];
+        if constexpr (t == 0) a = cmul(a, zr, zi);  // row 0 is read by lane 0 of pass 2, whose table row is W_32^n2: compensate
+        st4(EX + t * kExRowFloats + 4 * n2, a.x, a.y, b.x, b.y);
     });
 }
 
@@ -177,15 +190,11 @@ PSLA_HD void pair_pass1_store(int n2, const float* __restrict__ TWZ, float* __re
 //   b[brev4((k2 + 1) % 16)] = Z[kb + 32*k2]      (the W_16^n2 modulation rotates the output index)
 // ---------------------------------------------------------------------------------------------
 PSLA_HD void pair_pass2_fft(int t, const float* __restrict__ EX, const float* __restrict__ TW, cf (&a)[16], cf (&b)[16]) {
-    const int ka = t;
-    const int kb = (t != 0) ? 32 - t : 16;
-    const float* ra = EX + ka * kExRowFloats;
-    const float* rb = EX + kb * kExRowFloats;
-    const float* tw = TW + t * kExRowFloats;
-    static_for<0, 8>([&](auto q_) {
-        constexpr int n = 2 * decltype(q_)::value;
-        ld4(ra + 2 * n, a[n].x, a[n].y, a[n + 1].x, a[n + 1].y);
-        ld4(rb + 2 * n, b[n].x, b[n].y, b[n + 1].x, b[n + 1].y);
+    const float* row = EX + t * kExRowFloats;  // (Z1[t][n], Z1[32 - t][n]) for n = 0..15  (t = 0: rows 0 and 16)
+    const float* tw = TW + t * kTwRowFloats;
+    static_for<0, 16>([&](auto n_) {
+        constexpr int n = decltype(n_)::value;
+        ld4(row + 4 * n, a[n].x, a[n].y, b[n].x, b[n].y);
     });
     static_for<0, 8>([&](auto q_) {
         constexpr int n = 2 * decltype(q_)::value;

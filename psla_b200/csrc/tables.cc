@@ -96,8 +96,8 @@ bool build_table_buffer(const float* window, const float* mel_dense, int num_bin
     for (int t = 0; t < 16; ++t)
         for (int n2 = 0; n2 < 16; ++n2) {
             const double a = (t == 0) ? -two_pi * n2 / 32.0 : -two_pi * static_cast<double>((t * n2) % 512) / 512.0;
-            b[kTabTw + kExRowFloats * t + 2 * n2] = static_cast<float>(std::cos(a));
-            b[kTabTw + kExRowFloats * t + 2 * n2 + 1] = static_cast<float>(std::sin(a));
+            b[kTabTw + kTwRowFloats * t + 2 * n2] = static_cast<float>(std::cos(a));
+            b[kTabTw + kTwRowFloats * t + 2 * n2 + 1] = static_cast<float>(std::sin(a));
         }
     for (int n2 = 0; n2 < 16; ++n2) {
         const double a = two_pi * n2 / 32.0;

@@ -133,7 +133,7 @@ int emu_tables(int num_bins, float* window, float* mel_dense, float* tab, int ta
 // table offsets (floats) so the test can slice the buffer: win, tw, twz, mel_start, mel_bin, mel_info, mel_w, row strides
 void emu_layout(int* v) {
     v[0] = kTabWin; v[1] = kTabTw; v[2] = kTabTwz; v[3] = kTabMelStart; v[4] = kTabMelBin; v[5] = kTabMelInfo;
-    v[6] = kTabMelW; v[7] = kWinRow; v[8] = kExRowFloats;
+    v[6] = kTabMelW; v[7] = kWinRow; v[8] = kTwRowFloats;
 }
 
 // the register FFT templates alone against a direct DFT (N = 16, 32) and the pruned 32-point variant (n = -32:

@@ -622,6 +622,22 @@ __device__ __forceinline__ void epilogue(const StreamParams& p, const int* cs, c
         lb[i] = keep[i] ? p.log_bias : fill;
     }
     const int rows = min(kGroupFrames, p.T - f0);
+    if (FASTLOG) {
+        // straight-line: 16 independent cells (their MUFU / FMA latencies overlap), rows that are padding or time-masked by
+        // a select, rows past target_length by predicated stores -- no branch fences the scheduler
+#pragma unroll
+        for (int q = 0; q < kGroupFrames; ++q) {
+            const int row = f0 + q;
+            const bool rlive = row < m_eff && !(row >= t0 && row < t1);  // warp-uniform
+#pragma unroll
+            for (int i = 0; i < kMelSlots; ++i) {
+                float v = fmaf(lg2_ftz(fmaxf(acc[i][q], eps)), la[i], lb[i]);
+                v = rlive ? v : fill;
+                if (own[i] && q < rows) __stcs(col[i] + q * nmel, v);
+            }
+        }
+        return;
+    }
 #pragma unroll
     for (int q = 0; q < kGroupFrames; ++q) {
         if (q < rows) {  // warp-uniform
@@ -634,15 +650,9 @@ __device__ __forceinline__ void epilogue(const StreamParams& p, const int* cs, c
             } else {
 #pragma unroll
                 for (int i = 0; i < kMelSlots; ++i) {
-                    const float e = acc[i][q];
-                    float v;
-                    if (FASTLOG) {
-                        v = fmaf(lg2_ftz(fmaxf(e, eps)), la[i], lb[i]);
-                    } else {
-                        const float lg = logf(fmaxf(e, eps));
-                        v = p.skip_norm ? lg : __fdiv_rn(__fsub_rn(lg, p.norm_mean), p.norm_div);
-                        v = keep[i] ? v : fill;
-                    }
+                    const float lg = logf(fmaxf(acc[i][q], eps));
+                    float v = p.skip_norm ? lg : __fdiv_rn(__fsub_rn(lg, p.norm_mean), p.norm_div);
+                    v = keep[i] ? v : fill;
                     if (own[i]) __stcs(col[i] + q * nmel, v);
                 }
             }

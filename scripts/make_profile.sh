@@ -3,7 +3,7 @@
 # usage: bash scripts/make_profile.sh r01d
 set -e
 TAG=$1; OUT=profiles/$TAG; REP=gpurun_out/prof_stream.ncu-rep
-KEY=fbank_stream_kernelILb0ELb1ELb1EfE
+KEY=fbank_stream_kernelILb0ELb1ELb1EfLb0E
 mkdir -p $OUT /tmp/mkprof
 for f in bench.json bench_ref.json launches.csv lscpu.txt smi.txt; do cp gpurun_out/$f $OUT/; done
 [ -f gpurun_out/bench_n2.json ] && cp gpurun_out/bench_n2.json $OUT/

@@ -140,7 +140,9 @@ int psla_frontend_get_timing(psla_frontend_t* handle, double* stats_ms, double* 
  *   [4 + i]: i-th event: cycles since warp start | kind << 40 | groups in the step << 44; kinds 1..3 open a loop step
  *            (1 computed group, 2 computed group that staged its whole window, 3 run of constant groups), 4..9 mark
  *            phases inside it (4 clip entered, 5 window staged, 6 pass 1, 7 pass 2 + power, 8 mel, 9 epilogue done)
- * Pass NULL to switch it off. */
+ * Pass NULL to switch it off.  The timeline is compiled into separate kernel variants (the production kernels carry none
+ * of its checks) that exist for the default clip-mean mode only: forward() returns PSLA_E_UNSUPPORTED while a trace buffer is
+ * installed together with psla_frontend_set_exact_clip_mean(1). */
 int psla_frontend_set_trace(psla_frontend_t* handle, int64_t* device_buf, size_t capacity_records);
 int psla_frontend_trace_records(const psla_frontend_t* handle);
 int psla_frontend_trace_words(void);

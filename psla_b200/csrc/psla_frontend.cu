@@ -6,14 +6,15 @@
 // torchaudio.compliance.kaldi.fbank (torchaudio/compliance/kaldi.py:514-645).
 //
 // Kernels per forward():
-//   fbank_stream_kernel  persistent, one CTA of 16 autonomous warps per SM: every warp walks along its share of the
+//   fbank_stream_kernel  persistent, two CTAs of 8 autonomous warps per SM: every warp walks along its share of the
 //                        batch's frames 4 at a time -- stage 640 new (mixed, pre-emphasised) samples in its private
-//                        shared-memory window, two 512-point complex FFTs (one per half-warp, two real frames each),
-//                        power, sparse mel, log, SpecAugment fill, normalisation, 128-byte row stores
-//                        (see fbank_stream.cuh for the per-lane algorithm, stream_kernel.cuh for the kernel).
+//                        shared-memory window, two 512-point complex FFTs (one per half-warp, two real frames each) in
+//                        two-wide fp32 arithmetic, power, sparse mel, log, SpecAugment fill, normalisation, 128-byte row
+//                        stores (see fbank_stream.cuh for the per-lane algorithm, stream_kernel.cuh for the kernel).
 //   clip_stats_kernel    per-clip waveform sums (deterministic two-level reduction) for the whole-clip means of
 //                        audioset_dataset.py:92,98-99,117.  Launched only for clips that need them: all clips in
 //                        exact-clip-mean mode, otherwise only mixup clips whose partner is shorter.
+//   noise_roll_kernel    the optional noise / roll augmentation (audioset_dataset.py:197-199), a separate pass (noise_roll.cuh).
 // No cuFFT, no tensor cores (the mel projection is 504 non-zeros, not a dense contraction), no CPU path.
 #include <cuda_runtime.h>
 

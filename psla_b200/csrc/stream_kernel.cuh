@@ -158,6 +158,8 @@ struct Pcm<short> {
     }
 };
 
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 // 4 consecutive samples [i, i+4) of a waveform of n samples, zeros past the end
 template <class S>
 __device__ __forceinline__ typename Pcm<S>::reg_t load4(const S* __restrict__ w, int i, int n, bool aligned) {
@@ -854,6 +856,17 @@ __global__ void __launch_bounds__(kThreads, 2)
         const long long start_cost = find_start(ms, p.cm, p.n_clips, p.G, c_lo, lane, b, g);
         // groups are taken while the cost consumed is < budget
         if (lane == 0) cs_set_q(cs, CS_B, b, g, static_cast<int>(c_hi - start_cost), 0);
+        // pull the first group's window towards the SM while the tables are copied and the CTA barrier is passed: its
+        // loads (issued after the barrier) are the one DRAM latency of the launch nothing else hides.  No registers held.
+        if (b < p.n_clips) {
+            const ClipDesc d = ms.desc(b);
+            constexpr int kLine = 128 / static_cast<int>(sizeof(S));
+            const int s0 = g * kStepSamples + kLine * lane;
+            if (kLine * lane < kGroupSamples + kLine) {
+                if (s0 < d.n1) prefetch_l2(static_cast<const S*>(p.wav) + d.off1 + s0);
+                if (s0 < min(d.n1, d.n2)) prefetch_l2(static_cast<const S*>(p.wav) + d.off2 + s0);
+            }
+        }
     }
     {
         float4* dst = reinterpret_cast<float4*>(TAB);

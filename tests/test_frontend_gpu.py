@@ -473,3 +473,24 @@ def test_noise_roll_augmentation_matches_reference_getitem(FE, golden_dir):
 def PackedWavesOf(batch, device):
     from psla_b200.frontend import PackedWaves
     return PackedWaves(batch.waves.wav.to(device), batch.waves.offsets, batch.waves.lengths)
+
+
+@pytest.mark.parametrize("nmel", [64, 80, 40])
+def test_other_num_mel_bins(FE, nmel):
+    """`num_mel_bins` is an argument of the reference's dataset (audioset_dataset.py:63): sizes other than 128 take the
+    generic (run-time tap count) mel path, rows of `nmel` floats, and the scalar path of the noise / roll kernel."""
+    conf = {**CONF, "num_mel_bins": nmel, "target_length": 300}
+    fe = FE(conf)
+    waves = [synth_wave(700 + i, n) for i, n in enumerate((48000, 30000, 52345))]
+    src1, src2, lam = [0, 1, 2, 0], [-1, 0, -1, 2], [0.0, 0.45, 0.0, 0.7]
+    masks = [(0, 0, 0, 0), (5, min(20, nmel - 5), 40, 60), (nmel - 1, 1, 299, 1), (0, nmel // 2, 0, 0)]
+    out = fe(waves, src1, src2, lam, masks)
+    assert out.shape == (4, 300, nmel)
+    ref = O.batch_torch(waves, src1, src2, lam, masks, 300, MEAN, STD, num_mel_bins=nmel)
+    _check(out, ref, fill=_fill(), near_floor_below=-13.0)
+    scale, roll = np.array([0.3, 0.0, 0.9, 0.5]), np.array([-10, 9, 0, 3], np.int32)
+    field = torch.rand(4, 300, nmel)
+    got = fe.noise_roll(out, scale, roll, field).cpu()
+    want = torch.stack([torch.roll(out[b].cpu() + field[b] * float(np.float32(scale[b])) / 10, int(roll[b]), 0) for b in range(4)])
+    assert torch.equal(got, want)
+    fe.close()

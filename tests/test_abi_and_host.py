@@ -195,3 +195,14 @@ def test_bench_reference_arm_prints_one_json_line():
     assert d["impl"] == "reference" and d["unit"] == "clips/s" and d["higher_is_better"] is True and d["n_gpus"] == 1
     assert d["value"] > 0 and d["e2e"]["value"] == d["value"] and d["e2e"]["h2d_bytes_per_step"] == 0
     assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1 and "workload" in d["config"]
+
+
+def test_norm_stats_accumulator():
+    from psla_b200.dataloaders import NormStats, compute_norm_stats
+    torch.manual_seed(0)
+    xs = [torch.randn(3, 20, 8) * 4.5 - 4.6, torch.randn(2, 20, 8) * 4.5 - 4.6]
+    mean, std = compute_norm_stats([(xs[0], None), xs[1]])
+    allx = torch.cat([x.flatten() for x in xs]).double()
+    assert abs(mean - allx.mean().item()) < 1e-9 and abs(std - allx.std(unbiased=False).item()) < 1e-9
+    with pytest.raises(ValueError):
+        NormStats().result()

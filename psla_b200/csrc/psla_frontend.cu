@@ -640,13 +640,19 @@ int forward_any(psla_frontend_t* h, const void* wav, bool pcm16, const int64_t* 
         // reference's value.
         fast_log = h->fast_log;
         if (fast_log) {
-            float up = p.log_bias, dn = p.log_bias;
+            // candidates: the nominal bias moved in steps of half an ulp of the floor value (with skip_norm the nominal
+            // bias is 0, whose own neighbours are denormals and would never get there)
+            const float ulp = nextafterf(fabsf(p.floor_val), INFINITY) - fabsf(p.floor_val);
+            const float nominal = p.log_bias;
             bool found = false;
-            for (int k = 0; k < 64 && !found; ++k) {
-                if (fmaf(h->lg2_eps, p.log_scale, up) == p.floor_val) { p.log_bias = up; found = true; }
-                else if (fmaf(h->lg2_eps, p.log_scale, dn) == p.floor_val) { p.log_bias = dn; found = true; }
-                up = nextafterf(up, INFINITY);
-                dn = nextafterf(dn, -INFINITY);
+            for (int k = 0; k <= 64 && !found; ++k) {
+                for (int sgn = 1; sgn >= -1 && !found; sgn -= 2) {
+                    const float cand = nominal + static_cast<float>(sgn * k) * 0.5f * ulp;
+                    if (fmaf(h->lg2_eps, p.log_scale, cand) == p.floor_val) {
+                        p.log_bias = cand;
+                        found = true;
+                    }
+                }
             }
             if (!found) fast_log = 0;  // no such bias (never seen): the logf path evaluates the reference's expression verbatim
         }

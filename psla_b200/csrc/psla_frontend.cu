@@ -6,7 +6,7 @@
 // torchaudio.compliance.kaldi.fbank (torchaudio/compliance/kaldi.py:514-645).
 //
 // Kernels per forward():
-//   fbank_stream_kernel  persistent, two CTAs of 8 autonomous warps per SM: every warp walks along its share of the
+//   fbank_stream_kernel  persistent, four CTAs of 4 autonomous warps per SM: every warp walks along its share of the
 //                        batch's frames 4 at a time -- stage 640 new (mixed, pre-emphasised) samples in its private
 //                        shared-memory window, two 512-point complex FFTs (one per half-warp, two real frames each) in
 //                        two-wide fp32 arithmetic, power, sparse mel, log, SpecAugment fill, normalisation, 128-byte row
@@ -36,7 +36,7 @@
 using namespace psla;
 
 constexpr int kMetaSlots = 4;
-constexpr int kCtasPerSm = 2;  // __launch_bounds__(kThreads, 2): 8 warps x 128 registers and ~96 KB of shared memory per CTA
+constexpr int kCtasPerSm = 4;  // __launch_bounds__(kThreads, 4): 4 warps x 128 registers and ~51 KB of shared memory per CTA
 
 struct psla_frontend {
     int device = 0;
@@ -178,7 +178,7 @@ int upload_tables(psla_frontend* h) {
     if (!build_table_buffer(h->window.data(), h->mel_dense.data(), h->nmel, &buf, &spec)) return PSLA_E_UNSUPPORTED;
     const int total = static_cast<int>(buf.size());
     const size_t smem = (static_cast<size_t>(total) + static_cast<size_t>(kWarpsPerCta) * kWarpFloats) * sizeof(float);
-    if (kCtasPerSm * (smem + 1024) > 228 * 1024) return PSLA_E_UNSUPPORTED;  // two CTAs (tables + 8 warp windows each) must fit one SM
+    if (kCtasPerSm * (smem + 1024) > 228 * 1024) return PSLA_E_UNSUPPORTED;  // four CTAs (tables + 4 warp windows each) must fit one SM
     if (h->d_tab) {
         PSLA_CUDA(h, cudaDeviceSynchronize());
         cudaFree(h->d_tab);

@@ -42,7 +42,7 @@ constexpr CostModel kDefaultCost = {64, 2, 48};
 constexpr int kStatSegs = 8;  // partial sums per clip
 constexpr int kStatVals = 3;  // sum(w1), sum(w2), sum(w2[0:min(n1,n2)])
 
-constexpr int kWarpsPerCta = 8;   // two CTAs per SM
+constexpr int kWarpsPerCta = 4;   // four CTAs per SM
 constexpr int kThreads = kWarpsPerCta * 32;
 
 struct StreamParams {
@@ -818,12 +818,12 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
 }
 
 // ------------------------------------------------------------------------------------------------
-// Kernel 2: the streaming kernel.  grid = two CTAs per SM, block = 8 warps, no CTA barrier after the table load.
+// Kernel 2: the streaming kernel.  grid = four CTAs per SM, block = 4 warps, no CTA barrier after the table load.
 // Warp r of W owns the groups whose preceding cost lies in [r*C/W, (r+1)*C/W)  (clip-major order).
 // ------------------------------------------------------------------------------------------------
 // TRACE: the per-warp timeline (StreamParams::trace) is compiled in; the production variants carry none of its checks
 template <bool EXACT, bool MELSPEC, bool PMETA, class S, bool TRACE = false>
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(kThreads, 4)
     fbank_stream_kernel(const __grid_constant__ StreamParams p, const __grid_constant__ std::conditional_t<PMETA, MetaBlock, MetaNone> meta) {
     using MS = std::conditional_t<PMETA, ParamMeta, GlobalMeta>;
     MS ms;
@@ -871,7 +871,16 @@ __global__ void __launch_bounds__(kThreads, 2)
     {
         float4* dst = reinterpret_cast<float4*>(TAB);
         if (tid < n4) dst[tid] = tv;
-        for (int i = tid + kThreads; i < n4; i += kThreads) dst[i] = __ldg(tsrc + i);
+        // the rest in batches of 8 loads in flight per thread (one round trip to L2 per batch, not per float4)
+        for (int i0 = tid + kThreads; i0 < n4; i0 += 8 * kThreads) {
+            float4 t8[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (i0 + j * kThreads < n4) t8[j] = __ldg(tsrc + i0 + j * kThreads);
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (i0 + j * kThreads < n4) dst[i0 + j * kThreads] = t8[j];
+        }
     }
     __syncthreads();
     if (!has_work) {

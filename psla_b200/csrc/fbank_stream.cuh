@@ -107,8 +107,8 @@ static_assert(kPFloats <= kExFloats, "P must fit in the warp's exchange buffers"
 // per-warp shared-memory window (floats).  The exchange buffers ALIAS the staged samples from sample 256 on: once every
 // lane of the warp holds its pass-1 inputs in registers and the 240 samples shared with the next group have moved to
 // the front (stage_shift), the rest of D is dead until the next step commits its new samples -- by then the power
-// spectra (which alias EX) have been consumed by the mel stage.  10.7 KB per warp instead of 13.3 KB: two CTAs of 8
-// warps fit one SM, so the start-up of one launch overlaps the steady state of its neighbour.
+// spectra (which alias EX) have been consumed by the mel stage.  10.2 KB per warp instead of 13.3 KB: four CTAs of 4
+// warps (each with its own copy of the tables) fit one SM, so a following launch takes over SM resources in small steps.
 constexpr int kWsD = 0;
 constexpr int kWsEX = 256;  // >= kOverlapSamples (the part of D that survives the shift), multiple of 32 (same banks)
 constexpr int kWsBS = kWsEX + kExFloats;

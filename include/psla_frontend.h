@@ -118,6 +118,21 @@ int64_t psla_frontend_launch_count(const psla_frontend_t* handle);
 /* Select the log implementation: 0 = logf (default), 1 = lg2.approx based (abs err < 4e-6 on log-mel). */
 int psla_frontend_set_fast_log(psla_frontend_t* handle, int enable);
 
+/* Output layout of the forward entry points (the consumer, src/models/Models.py:104-107, turns the
+ * dataset's [B, T, F] into [B, 1, F, T] with unsqueeze(1).transpose(2, 3) before its first convolution; under autocast it
+ * is then cast to a 16-bit type).  With a frequency-major layout the kernel writes what that convolution reads:
+ *   PSLA_OUT_TF_F32   fp32 [n_clips, target_length, num_mel_bins]   the reference's (default)
+ *   PSLA_OUT_FT_F32   fp32 [n_clips, num_mel_bins, target_length]   == out_tf.transpose(1, 2), bit for bit
+ *   PSLA_OUT_FT_BF16  bf16 [n_clips, num_mel_bins, target_length]   == the same, rounded to nearest-even
+ * The frequency-major layouts need num_mel_bins == 128, target_length % 4 == 0 and a 16-byte aligned `out`, and are not
+ * available together with exact_clip_mean or the timeline (PSLA_E_UNSUPPORTED at the forward call otherwise).  `out` /
+ * `out_host` keep their `float*` type in the signatures; for PSLA_OUT_FT_BF16 they point to n_clips * 128 *
+ * target_length 16-bit elements.  psla_frontend_noise_roll works on the default layout only. */
+#define PSLA_OUT_TF_F32 0
+#define PSLA_OUT_FT_F32 1
+#define PSLA_OUT_FT_BF16 2
+int psla_frontend_set_output_layout(psla_frontend_t* handle, int layout);
+
 /* Whole-clip DC removal (audioset_dataset.py:92 / :98-99 / :117).  Every constant the reference subtracts from a whole
  * clip is removed again by kaldi.fbank's per-frame DC removal (kaldi.py:183-186), so the default (0) subtracts the
  * clip's first sample instead of its mean -- same features up to fp32 rounding, no extra pass over the waveform; clip

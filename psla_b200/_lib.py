@@ -41,6 +41,7 @@ SYMBOLS = {
     "psla_frontend_launch_count": (c_int64, [c_void_p]),
     "psla_frontend_set_fast_log": (c_int, [c_void_p, c_int]),
     "psla_frontend_set_exact_clip_mean": (c_int, [c_void_p, c_int]),
+    "psla_frontend_set_output_layout": (c_int, [c_void_p, c_int]),
     "psla_frontend_set_timing": (c_int, [c_void_p, c_int]),
     "psla_frontend_get_timing": (c_int, [c_void_p, POINTER(c_double), POINTER(c_double), POINTER(c_int64)]),
     "psla_frontend_set_trace": (c_int, [c_void_p, c_void_p, c_size_t]),

@@ -52,6 +52,7 @@ struct psla_frontend {
     int fast_log = 0;
     float lg2_eps = -23.0f;  // what the device's lg2.approx returns for the float epsilon (probed once in create())
     int exact_mean = 0;
+    int layout = PSLA_OUT_TF_F32;
     bool mel_spec = false;
     int num_sms = 0;
     int timing = 0;
@@ -131,12 +132,12 @@ int probe_lg2_eps(psla_frontend* h) {
     return PSLA_OK;
 }
 
-template <bool EXACT, bool MELSPEC, bool PMETA, class S, bool TRACE>
+template <bool EXACT, bool MELSPEC, bool PMETA, class S, bool TRACE, int OUT = kOutTF>
 cudaError_t prepare_one(size_t smem) {
-    cudaError_t e = cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC, PMETA, S, TRACE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC, PMETA, S, TRACE, OUT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          static_cast<int>(smem));
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC, PMETA, S, TRACE>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+    return cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC, PMETA, S, TRACE, OUT>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
 }
 template <bool EXACT, bool MELSPEC, bool TRACE>
 cudaError_t prepare_kernel(size_t smem) {
@@ -147,11 +148,29 @@ cudaError_t prepare_kernel(size_t smem) {
     return e;
 }
 
-// launch of the variant selected at run time (the tracing variants exist for the default clip-mean mode only)
+template <int OUT>
+cudaError_t prepare_layout(size_t smem) {
+    cudaError_t e = prepare_one<false, true, false, float, false, OUT>(smem);
+    if (e == cudaSuccess) e = prepare_one<false, true, true, float, false, OUT>(smem);
+    if (e == cudaSuccess) e = prepare_one<false, true, false, short, false, OUT>(smem);
+    if (e == cudaSuccess) e = prepare_one<false, true, true, short, false, OUT>(smem);
+    return e;
+}
+
+// launch of the variant selected at run time (the tracing variants exist for the default clip-mean mode only, the
+// frequency-major layouts for the default mode without tracing and 128 mel bins)
 template <class S>
-cudaError_t launch_stream_kernel(const cudaLaunchConfig_t& cfg, bool exact, bool spec, bool pmeta, bool trace, const StreamParams& p,
-                                 const MetaBlock& mb) {
+cudaError_t launch_stream_kernel(const cudaLaunchConfig_t& cfg, bool exact, bool spec, bool pmeta, bool trace, int layout,
+                                 const StreamParams& p, const MetaBlock& mb) {
     const MetaNone none = {0};
+    if (layout == PSLA_OUT_FT_F32) {
+        if (pmeta) return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, true, true, S, false, kOutFT>, p, mb);
+        return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, true, false, S, false, kOutFT>, p, none);
+    }
+    if (layout == PSLA_OUT_FT_BF16) {
+        if (pmeta) return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, true, true, S, false, kOutFTbf16>, p, mb);
+        return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, true, false, S, false, kOutFTbf16>, p, none);
+    }
     if (trace) {
         switch ((spec ? 2 : 0) | (pmeta ? 1 : 0)) {
             case 0: return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, false, false, S, true>, p, none);
@@ -195,6 +214,8 @@ int upload_tables(psla_frontend* h) {
     PSLA_CUDA(h, (prepare_kernel<true, true, false>(smem)));
     PSLA_CUDA(h, (prepare_kernel<false, false, true>(smem)));
     PSLA_CUDA(h, (prepare_kernel<false, true, true>(smem)));
+    PSLA_CUDA(h, prepare_layout<kOutFT>(smem));
+    PSLA_CUDA(h, prepare_layout<kOutFTbf16>(smem));
     PSLA_CUDA(h, cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, h->device));
     return PSLA_OK;
 }
@@ -325,6 +346,7 @@ int psla_frontend_noise_roll(psla_frontend_t* h, const float* in, float* out, co
                              const int32_t* shift, int n_clips, int target_length, uint64_t seed, void* stream_) {
     if (!h || !in || !out || !scale || !shift || n_clips < 0 || target_length < 1 || in == out) return PSLA_E_INVALID;
     if (n_clips == 0) return PSLA_OK;
+    if (h->layout != PSLA_OUT_TF_F32) return PSLA_E_UNSUPPORTED;  // rows are rolled: [B, T, F] only
     const size_t bytes = static_cast<size_t>(n_clips) * target_length * h->nmel * sizeof(float);
     const char *a = reinterpret_cast<const char*>(in), *b = reinterpret_cast<const char*>(out);
     if (a < b + bytes && b < a + bytes) return PSLA_E_INVALID;  // a roll cannot run in place
@@ -442,9 +464,17 @@ int psla_frontend_set_exact_clip_mean(psla_frontend_t* h, int enable) {
     return PSLA_OK;
 }
 
+int psla_frontend_set_output_layout(psla_frontend_t* h, int layout) {
+    if (!h || layout < PSLA_OUT_TF_F32 || layout > PSLA_OUT_FT_BF16) return PSLA_E_INVALID;
+    h->layout = layout;
+    return PSLA_OK;
+}
+
 }  // extern "C"
 
 namespace {
+size_t out_elem_bytes(const psla_frontend* h) { return h->layout == PSLA_OUT_FT_BF16 ? 2 : 4; }
+
 int forward_any(psla_frontend_t* h, const void* wav, bool pcm16, const int64_t* wav_offset, const int64_t* wav_length, int n_wav,
                 const int32_t* src1, const int32_t* src2, const double* lambda, const int32_t* mask, int n_clips, int target_length,
                 float norm_mean, float norm_div, int skip_norm, float* out, void* workspace, size_t workspace_bytes, void* stream_) {
@@ -456,6 +486,10 @@ int forward_any(psla_frontend_t* h, const void* wav, bool pcm16, const int64_t* 
     const size_t need = psla_frontend_workspace_bytes(h, n_clips);
     if (!workspace || workspace_bytes < need || (reinterpret_cast<uintptr_t>(workspace) & 255)) return PSLA_E_WORKSPACE;
     if (!skip_norm && !(norm_div != 0.f)) return PSLA_E_INVALID;
+    if (h->layout != PSLA_OUT_TF_F32) {  // frequency-major: a group's 4 frames of a bin are one aligned vector store
+        if (!h->mel_spec || h->nmel != kMaxMel || (target_length % kGroupFrames) != 0 || h->exact_mean || h->trace) return PSLA_E_UNSUPPORTED;
+        if (reinterpret_cast<uintptr_t>(out) & 15) return PSLA_E_INVALID;
+    }
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
 
     DeviceGuard guard(h->device);
@@ -666,7 +700,7 @@ int forward_any(psla_frontend_t* h, const void* wav, bool pcm16, const int64_t* 
     // Overlap with the previous forward() of this handle (its tail SMs start this launch's CTAs) when nothing can
     // conflict: same stream, no statistics kernel in between, disjoint output ranges, no tracing.
     const char* out_lo = reinterpret_cast<const char*>(out);
-    const char* out_hi = out_lo + static_cast<size_t>(n_clips) * target_length * h->nmel * sizeof(float);
+    const char* out_hi = out_lo + static_cast<size_t>(n_clips) * target_length * h->nmel * out_elem_bytes(h);
     const bool overlap_ok = h->pdl && param_meta && !h->trace && !h->timing && h->prev_valid && h->prev_stream == stream_ &&
                             (out_hi <= h->prev_out_lo || out_lo >= h->prev_out_hi);
     h->prev_valid = true;
@@ -685,8 +719,8 @@ int forward_any(psla_frontend_t* h, const void* wav, bool pcm16, const int64_t* 
     cfg.numAttrs = overlap_ok ? 1 : 0;
     const bool trace = h->trace != nullptr;
     if (trace && h->exact_mean) return PSLA_E_UNSUPPORTED;  // the timeline is compiled for the default clip-mean mode only
-    const cudaError_t le = pcm16 ? launch_stream_kernel<short>(cfg, h->exact_mean, h->mel_spec, param_meta, trace, p, h->meta_host)
-                                 : launch_stream_kernel<float>(cfg, h->exact_mean, h->mel_spec, param_meta, trace, p, h->meta_host);
+    const cudaError_t le = pcm16 ? launch_stream_kernel<short>(cfg, h->exact_mean, h->mel_spec, param_meta, trace, h->layout, p, h->meta_host)
+                                 : launch_stream_kernel<float>(cfg, h->exact_mean, h->mel_spec, param_meta, trace, h->layout, p, h->meta_host);
     PSLA_CUDA(h, le);
     PSLA_CUDA(h, cudaGetLastError());
     if (slot) {
@@ -716,7 +750,7 @@ int forward_host_any(psla_frontend_t* h, const void* wav_host, bool pcm16, const
     }
     if (total < 1) return PSLA_E_INVALID;
     const size_t wav_bytes = static_cast<size_t>(total) * (pcm16 ? sizeof(int16_t) : sizeof(float));
-    const size_t out_bytes = static_cast<size_t>(n_clips) * target_length * h->nmel * sizeof(float);
+    const size_t out_bytes = static_cast<size_t>(n_clips) * target_length * h->nmel * out_elem_bytes(h);
     const size_t ws_bytes = psla_frontend_workspace_bytes(h, n_clips);
     auto grow = [&](void** ptr, size_t* cap, size_t need) -> int {
         if (*cap >= need) return PSLA_OK;

@@ -2,11 +2,15 @@
 // (Host side / C ABI: psla_frontend.cu.  Per-lane FFT / mel phases: fbank_stream.cuh.)
 #pragma once
 
+#include <cuda_bf16.h>
 #include <cuda_runtime.h>
 
 #include "fbank_stream.cuh"
 
 namespace psla {
+
+// output layouts (psla_frontend_set_output_layout): values of PSLA_OUT_* in include/psla_frontend.h
+constexpr int kOutTF = 0, kOutFT = 1, kOutFTbf16 = 2;
 
 // ------------------------------------------------------------------------------------------------
 // Device-side data
@@ -662,6 +666,64 @@ __device__ __forceinline__ void epilogue(const StreamParams& p, const int* cs, c
     }
 }
 
+// ---- frequency-major output (the layout the model's first convolution consumes: Models.py:106-107 turns [B, T, F] into
+// [B, 1, F, T] with unsqueeze + transpose) -- OUT = 1: fp32 [B, F, T], OUT = 2: bf16 [B, F, T].  target_length is a multiple
+// of 4 here (checked on the host), so a group's 4 frames of one mel bin are ONE aligned 16-byte (8-byte) store and no
+// row is cut: a lane writes its 4 bins with 4 vector stores instead of 16 scalar ones.  Same arithmetic, same values.
+template <bool BF16>
+__device__ __forceinline__ void store_frames4(void* __restrict__ clip_out, size_t elem, float v0, float v1, float v2, float v3) {
+    if (BF16) {
+        const __nv_bfloat162 lo = __float22bfloat162_rn(make_float2(v0, v1)), hi = __float22bfloat162_rn(make_float2(v2, v3));
+        uint2 u;
+        u.x = *reinterpret_cast<const unsigned*>(&lo);
+        u.y = *reinterpret_cast<const unsigned*>(&hi);
+        __stcs(reinterpret_cast<uint2*>(static_cast<__nv_bfloat16*>(clip_out) + elem), u);
+    } else {
+        __stcs(reinterpret_cast<float4*>(static_cast<float*>(clip_out) + elem), make_float4(v0, v1, v2, v3));
+    }
+}
+// rows [row0, row1) of every mel bin of one clip := v  (row0, row1 multiples of 4)
+template <bool BF16>
+__device__ __forceinline__ void warp_fill_ft(void* __restrict__ clip_out, int T, int nmel, int row0, int row1, float v, int lane) {
+    const int n4 = (row1 - row0) >> 2;
+    const int total = nmel * n4;
+    for (int i = lane; i < total; i += 32) {
+        const int m = i / n4, j = i - m * n4;
+        store_frames4<BF16>(clip_out, static_cast<size_t>(m) * T + row0 + 4 * j, v, v, v, v);
+    }
+}
+template <bool FASTLOG, int NMEL, bool BF16>
+__device__ __forceinline__ void epilogue_ft(const StreamParams& p, const int* cs, const int* mel_bin, int lane, int f0, void* __restrict__ clip_out,
+                                            const float (&acc)[kMelSlots][kGroupFrames]) {
+    const float eps = 1.1920928955078125e-07f;  // kaldi.py:22
+    const float fill = p.fill;
+    const int4 mq = cs_q(cs, CS_F0);
+    const int mf0 = mq.x, mf1 = mq.y, t0 = mq.z, t1 = mq.w, m_eff = cs_i(cs, CS_MEFF);
+    bool rlive[kGroupFrames];  // warp-uniform
+#pragma unroll
+    for (int q = 0; q < kGroupFrames; ++q) rlive[q] = f0 + q < m_eff && !(f0 + q >= t0 && f0 + q < t1);
+#pragma unroll
+    for (int i = 0; i < kMelSlots; ++i) {
+        const int mb = mel_bin[32 * i + lane];
+        const bool own = NMEL != 0 || mb >= 0;
+        const bool keep = !(mb >= mf0 && mb < mf1);
+        const float la = keep ? p.log_scale : 0.f, lb = keep ? p.log_bias : fill;
+        float v[kGroupFrames];
+#pragma unroll
+        for (int q = 0; q < kGroupFrames; ++q) {
+            if (FASTLOG) {
+                v[q] = fmaf(lg2_ftz(fmaxf(acc[i][q], eps)), la, lb);
+            } else {
+                const float lg = logf(fmaxf(acc[i][q], eps));
+                v[q] = p.skip_norm ? lg : __fdiv_rn(__fsub_rn(lg, p.norm_mean), p.norm_div);
+                v[q] = keep ? v[q] : fill;
+            }
+            v[q] = rlive[q] ? v[q] : fill;
+        }
+        if (own) store_frames4<BF16>(clip_out, static_cast<size_t>(max(mb, 0)) * p.T + f0, v[0], v[1], v[2], v[3]);
+    }
+}
+
 __device__ __forceinline__ void cs_set(int* cs, int w, int v, int lane) {
     if (lane == 0) *reinterpret_cast<volatile int*>(cs + w) = v;
 }
@@ -742,7 +804,7 @@ constexpr int kStageIters = StageGeom<kOverlapSamples, kGroupSamples>::kIters;  
 // one live group whose window is staged: frame means, pass 1, (shift), pass 2, power, (prefetch), mel, epilogue.
 // Everything it needs beyond the kernel parameters comes from the warp's shared-memory state (CS_*).  The prefetch
 // leaves the next group's 640 new samples in ra / rc; the caller commits them at the top of its next step.
-template <bool MELSPEC, class S, bool TRACE>
+template <bool MELSPEC, class S, bool TRACE, int OUT>
 __device__ __forceinline__ void process_group(const StreamParams& p, const float* TAB, float* WS, int lane, const int b, const int gn,
                                               typename Pcm<S>::reg_t (&ra)[kStageIters], typename Pcm<S>::reg_t (&rc)[kStageIters]) {
     float* D = WS + kWsD;
@@ -808,11 +870,18 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
     if (TRACE && p.trace) trace_phase(p, cs, lane, 8);
     {
         const int f0 = (gn >> 2) * kGroupFrames;
-        float* out = p.out + static_cast<size_t>(b) * p.T * p.nmel;
         const int* mel_bin = reinterpret_cast<const int*>(TAB + kTabMelBin);
         // MELSPEC is only selected for 128 mel bins: every (slot, lane) then owns a column
-        if (p.fast_log) epilogue<true, MELSPEC ? kMaxMel : 0>(p, cs, mel_bin, lane, f0, out, acc);
-        else epilogue<false, MELSPEC ? kMaxMel : 0>(p, cs, mel_bin, lane, f0, out, acc);
+        if constexpr (OUT == kOutTF) {
+            float* out = p.out + static_cast<size_t>(b) * p.T * p.nmel;
+            if (p.fast_log) epilogue<true, MELSPEC ? kMaxMel : 0>(p, cs, mel_bin, lane, f0, out, acc);
+            else epilogue<false, MELSPEC ? kMaxMel : 0>(p, cs, mel_bin, lane, f0, out, acc);
+        } else {
+            constexpr bool BF16 = OUT == kOutFTbf16;
+            void* out = reinterpret_cast<char*>(p.out) + static_cast<size_t>(b) * p.T * p.nmel * (BF16 ? 2 : 4);
+            if (p.fast_log) epilogue_ft<true, MELSPEC ? kMaxMel : 0, BF16>(p, cs, mel_bin, lane, f0, out, acc);
+            else epilogue_ft<false, MELSPEC ? kMaxMel : 0, BF16>(p, cs, mel_bin, lane, f0, out, acc);
+        }
     }
     if (TRACE && p.trace) trace_phase(p, cs, lane, 9);
 }
@@ -822,7 +891,8 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
 // Warp r of W owns the groups whose preceding cost lies in [r*C/W, (r+1)*C/W)  (clip-major order).
 // ------------------------------------------------------------------------------------------------
 // TRACE: the per-warp timeline (StreamParams::trace) is compiled in; the production variants carry none of its checks
-template <bool EXACT, bool MELSPEC, bool PMETA, class S, bool TRACE = false>
+// OUT: output layout (kOutTF: fp32 [B, T, F], the reference's; kOutFT / kOutFTbf16: [B, F, T] for the model's first convolution)
+template <bool EXACT, bool MELSPEC, bool PMETA, class S, bool TRACE = false, int OUT = kOutTF>
 __global__ void __launch_bounds__(kThreads, 4)
     fbank_stream_kernel(const __grid_constant__ StreamParams p, const __grid_constant__ std::conditional_t<PMETA, MetaBlock, MetaNone> meta) {
     using MS = std::conditional_t<PMETA, ParamMeta, GlobalMeta>;
@@ -916,7 +986,13 @@ __global__ void __launch_bounds__(kThreads, 4)
             const int n = min(run_end - g, (budget + p.cm.dead - 1) / p.cm.dead);
             if (TRACE && p.trace) trace_count(p, cs, lane, CS_TR_DEAD, n);
             const int row0 = kGroupFrames * g, row1 = min(p.T, kGroupFrames * (g + n));
-            warp_fill(p.out + (static_cast<size_t>(b) * p.T + row0) * p.nmel, static_cast<long long>(row1 - row0) * p.nmel, p.fill, lane);
+            if constexpr (OUT == kOutTF) {
+                warp_fill(p.out + (static_cast<size_t>(b) * p.T + row0) * p.nmel, static_cast<long long>(row1 - row0) * p.nmel, p.fill, lane);
+            } else {
+                constexpr bool BF16 = OUT == kOutFTbf16;
+                warp_fill_ft<BF16>(reinterpret_cast<char*>(p.out) + static_cast<size_t>(b) * p.T * p.nmel * (BF16 ? 2 : 4), p.T, p.nmel, row0, row1,
+                                   p.fill, lane);
+            }
             const bool wrap = g + n == p.G;
             budget -= n * p.cm.dead;
             b = wrap ? b + 1 : b;
@@ -971,7 +1047,7 @@ __global__ void __launch_bounds__(kThreads, 4)
             if (lane == 0) cs[CS_CARRY] = __float_as_int(carry);
         }
         __syncwarp();
-        process_group<MELSPEC, S, TRACE>(p, TAB, WS, lane, b, gn, ra, rc);
+        process_group<MELSPEC, S, TRACE, OUT>(p, TAB, WS, lane, b, gn, ra, rc);
         staged = next_live;
         {  // advance
             const bool wrap = g + 1 == p.G;

@@ -20,6 +20,7 @@ import torch
 from . import _lib, tables
 
 SAMPLE_RATE = 16000
+OUTPUT_LAYOUTS = {"tf": 0, "ft": 1, "ft_bf16": 2}  # PSLA_OUT_TF_F32 / PSLA_OUT_FT_F32 / PSLA_OUT_FT_BF16
 
 
 @dataclass
@@ -117,6 +118,7 @@ class GpuFbankFrontend:
             raise ValueError("tables_from must be 'torch' or 'native'")
         self.set_fast_log(fast_log)
         self.set_exact_clip_mean(exact_clip_mean)
+        self.output_layout = "tf"
         self._ws = {}
 
     # ---- lifetime ----
@@ -141,6 +143,23 @@ class GpuFbankFrontend:
         True: clip means from a statistics kernel, the reference's fp32 expression verbatim."""
         self.exact_clip_mean = bool(enable)
         _lib.check(self.lib.psla_frontend_set_exact_clip_mean(self._h, int(self.exact_clip_mean)), "set_exact_clip_mean", self._h)
+
+    def set_output_layout(self, layout: str = "tf"):
+        """Layout of the features the forward calls write (psla_frontend_set_output_layout):
+          "tf"       float32  [B, T, F]  what the reference's dataset returns (default)
+          "ft"       float32  [B, F, T]  == tf.transpose(1, 2) bit for bit: `x.unsqueeze(1)` is the [B, 1, F, T] the model's
+                                         first convolution reads (Models.py:106-107 does unsqueeze(1).transpose(2, 3))
+          "ft_bf16"  bfloat16 [B, F, T]  the same, rounded to nearest-even (what autocast would cast it to)
+        The frequency-major layouts need 128 mel bins and target_length % 4 == 0."""
+        if layout not in OUTPUT_LAYOUTS:
+            raise ValueError(f"layout must be one of {sorted(OUTPUT_LAYOUTS)}")
+        _lib.check(self.lib.psla_frontend_set_output_layout(self._h, OUTPUT_LAYOUTS[layout]), "set_output_layout", self._h)
+        self.output_layout = layout
+
+    def out_shape_dtype(self, B: int, T: int):
+        if self.output_layout == "tf":
+            return (B, T, self.num_mel_bins), torch.float32
+        return (B, self.num_mel_bins, T), (torch.bfloat16 if self.output_layout == "ft_bf16" else torch.float32)
 
     def set_timing(self, enable: bool):
         _lib.check(self.lib.psla_frontend_set_timing(self._h, int(bool(enable))), "set_timing", self._h)
@@ -210,10 +229,11 @@ class GpuFbankFrontend:
         if not wav.is_cuda:
             raise ValueError("forward_packed needs device-resident waveforms; use forward_host for host buffers")
         B = len(src1)
+        shape, dtype = self.out_shape_dtype(B, T)
         if out is None:
-            out = torch.empty((B, T, self.num_mel_bins), dtype=torch.float32, device=self.device)
-        elif tuple(out.shape) != (B, T, self.num_mel_bins) or out.dtype != torch.float32 or not out.is_contiguous():
-            raise ValueError("out must be a contiguous float32 [B, T, F] cuda tensor")
+            out = torch.empty(shape, dtype=dtype, device=self.device)
+        elif tuple(out.shape) != shape or out.dtype != dtype or not out.is_contiguous() or not out.is_cuda:
+            raise ValueError(f"out must be a contiguous {dtype} {list(shape)} cuda tensor (output layout '{self.output_layout}')")
         if B == 0:
             return out
         ao, p_off = _as_c(packed.offsets, np.int64, ctypes.c_int64)
@@ -278,9 +298,10 @@ class GpuFbankFrontend:
         am, pm = _as_c(None if masks is None else np.asarray(masks).reshape(B, 4), np.int32, ctypes.c_int32)
         s = (stream or torch.cuda.current_stream(self.device)).cuda_stream
         out_ptr = None
+        shape, dtype = self.out_shape_dtype(B, T)
         if out_host is not None:
-            if tuple(out_host.shape) != (B, T, self.num_mel_bins) or out_host.dtype != torch.float32 or out_host.is_cuda:
-                raise ValueError("out_host must be a host float32 [B, T, F] tensor")
+            if tuple(out_host.shape) != shape or out_host.dtype != dtype or out_host.is_cuda or not out_host.is_contiguous():
+                raise ValueError(f"out_host must be a contiguous host {dtype} {list(shape)} tensor (output layout '{self.output_layout}')")
             out_ptr = out_host.data_ptr()
         if wav.dtype not in (torch.float32, torch.int16):
             raise ValueError("waveforms must be float32 or int16 PCM")
@@ -291,7 +312,10 @@ class GpuFbankFrontend:
         _lib.check(st, "psla_frontend_forward_host", self._h)
         if out_host is not None:
             return out_host
-        return _DeviceView(self.lib.psla_frontend_device_out(self._h), (B, T, self.num_mel_bins), self.device).tensor()
+        if dtype == torch.bfloat16:  # the array interface has no bf16: view the 16-bit words, reinterpret
+            v = _DeviceView(self.lib.psla_frontend_device_out(self._h), shape, self.device, "<i2").tensor()
+            return v.view(torch.bfloat16)
+        return _DeviceView(self.lib.psla_frontend_device_out(self._h), shape, self.device).tensor()
 
     def __call__(self, waves, src1=None, src2=None, lam=None, masks=None, **kw) -> torch.Tensor:
         """waves: PackedWaves or a sequence of [1, n] / [n] tensors.  src1 defaults to one clip per waveform."""
@@ -307,9 +331,9 @@ class GpuFbankFrontend:
 class _DeviceView:
     """Zero-copy torch view of a library-owned device buffer (via __cuda_array_interface__)."""
 
-    def __init__(self, ptr: int, shape, device):
+    def __init__(self, ptr: int, shape, device, typestr: str = "<f4"):
         self._device = device
-        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f4", "data": (int(ptr), False),
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False),
                                          "version": 3, "strides": None}
 
     def tensor(self) -> torch.Tensor:

@@ -494,3 +494,63 @@ def test_other_num_mel_bins(FE, nmel):
     want = torch.stack([torch.roll(out[b].cpu() + field[b] * float(np.float32(scale[b])) / 10, int(roll[b]), 0) for b in range(4)])
     assert torch.equal(got, want)
     fe.close()
+
+
+@pytest.mark.parametrize("fast_log", [False, True])
+@pytest.mark.parametrize("pcm16", [False, True])
+def test_frequency_major_output_layouts(FE, fast_log, pcm16):
+    """the consumer turns [B, T, F] into [B, 1, F, T] (src/models/Models.py:106-107) and autocast casts it
+    to 16 bits; the "ft" / "ft_bf16" layouts write that directly.  Same arithmetic as the default layout: the fp32
+    result is its transpose bit for bit, the bf16 one its round-to-nearest-even -- and the default layout is what the
+    oracle checks.  Batches below and above the parameter-space descriptor limit (128 clips), masks, padding, mixup."""
+    from psla_b200.frontend import pack_waveforms, to_pcm16, PackedWaves
+    fe = FE(CONF, fast_log=fast_log)
+    waves = [synth_wave(900 + i, n, kind) for i, (n, kind) in enumerate(
+        ((160000, "gauss"), (160000, "am"), (100000, "int16"), (200000, "gauss"), (5000, "gauss"), (400, "gauss")))]
+    packed = pack_waveforms(waves, device=fe.device)
+    if pcm16:
+        packed = PackedWaves(to_pcm16(packed.wav), packed.offsets, packed.lengths)
+    for B in (7, 140):
+        src1 = [b % 6 for b in range(B)]
+        src2 = [{0: 1, 2: 3}.get(b % 6, -1) for b in range(B)]  # equal-length and longer (cut) partners: descriptors as kernel parameters
+        if B > 128:
+            src2[1] = 4  # a shorter partner (zero-padded tail) => clip statistics kernel + uploaded descriptors
+        lam = [0.3 + 0.001 * b for b in range(B)]
+        torch.manual_seed(B)
+        masks = [O.draw_mask_offsets(48, 192, 128, 1056) for _ in range(B)]
+        masks[0] = (0, 0, 0, 0)
+        masks[2] = (0, 128, 0, 0)
+        masks[3] = (100, 28, 1052, 4)
+        fe.set_output_layout("tf")
+        tf = fe.forward_packed(packed, src1, src2, lam, masks).cpu()
+        fe.set_output_layout("ft")
+        ft = fe.forward_packed(packed, src1, src2, lam, masks)
+        assert ft.shape == (B, 128, 1056) and ft.dtype == torch.float32
+        assert torch.equal(ft.cpu(), tf.transpose(1, 2))
+        fe.set_output_layout("ft_bf16")
+        fb = fe.forward_packed(packed, src1, src2, lam, masks)
+        assert fb.shape == (B, 128, 1056) and fb.dtype == torch.bfloat16
+        assert torch.equal(fb.cpu(), tf.transpose(1, 2).to(torch.bfloat16))
+        if B == 7 and not pcm16:  # and directly against the oracle
+            ref = O.batch_torch(waves, src1, src2, lam, masks, 1056, MEAN, STD)
+            _check(ft.transpose(1, 2).contiguous(), ref, fill=_fill(), near_floor_below=-13.0)
+            # host entry point: pinned in, pinned out, 16-bit elements
+            host = PackedWaves(packed.wav.cpu().pin_memory(), packed.offsets, packed.lengths)
+            out_host = torch.empty(B, 128, 1056, dtype=torch.bfloat16).pin_memory()
+            fe.forward_host(host, src1, src2, lam, masks, out_host=out_host)
+            torch.cuda.synchronize()
+            assert torch.equal(out_host, fb.cpu())
+            assert torch.equal(fe.forward_host(host, src1, src2, lam, masks).cpu(), fb.cpu())
+    # what the layouts cannot do is an error at the call, not a wrong result
+    with pytest.raises(Exception):
+        fe.forward_packed(packed, [0], None, None, None, target_length=1054)
+    with pytest.raises(Exception):
+        fe.noise_roll(torch.zeros(1, 1056, 128, device=fe.device), [0.1], [1])
+    fe.set_output_layout("tf")
+    assert fe.forward_packed(packed, [0], None, None, None, target_length=1054).shape == (1, 1054, 128)
+    fe.close()
+    fe64 = FE({**CONF, "num_mel_bins": 64})
+    fe64.set_output_layout("ft")
+    with pytest.raises(Exception):
+        fe64.forward_packed(packed, [0], None, None, None)
+    fe64.close()

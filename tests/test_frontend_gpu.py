@@ -364,8 +364,13 @@ def test_size_independent_properties_at_full_size(fe):
     assert ((full[0, :500] - pre[0, :500]).abs() * STD).max() <= TOL  # clip mean differs -> rounding only
     sh = fe([x[:, 1600:]]).cpu()  # 10 frames later
     assert ((full[0, 10:998] - sh[0, :988]).abs() * STD).max() <= TOL
+    # x + 0.25 re-quantises the input (ulp 3e-8 instead of <= 7.5e-9): two evaluations of different fp32 inputs, each within
+    # TOL of the exact features of its own input => their difference is bounded by 2 TOL (observed: 0.6e-3 .. 1.0e-3 on the
+    # weakest cell of the clip, depending on the rounding order of the kernel version), and by TOL for all but a few cells
     dc = fe([x + 0.25]).cpu()
-    assert ((full - dc).abs() * STD).max() <= TOL
+    d = (full - dc).abs() * STD
+    assert d.max() <= 2 * TOL
+    assert (d > TOL).sum().item() <= 3
 
 
 def test_dataset_drop_in_matches_reference_getitem(FE, golden_dir):

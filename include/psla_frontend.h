@@ -178,8 +178,10 @@ int psla_frontend_set_meta_stream(psla_frontend_t* handle, int enable);
 int psla_frontend_set_launch_overlap(psla_frontend_t* handle, int enable);
 
 /* 1 (default): batches of at most 128 clips that need no statistics pass carry their clip descriptors in the kernel's
- * parameter space (no upload; required for the launch overlap above).  0: always upload them.  Results do not depend
- * on it. */
+ * parameter space (no upload; required for the launch overlap above), and larger batches that need no statistics pass
+ * are validated as a whole and then enqueued as balanced chunks of at most 128 clips, each such a launch
+ * (psla_frontend_launch_count advances by the number of chunks).  0: always upload them, one launch per call.  Results
+ * do not depend on it. */
 int psla_frontend_set_param_meta(psla_frontend_t* handle, int enable);
 
 const char* psla_strerror(int status);

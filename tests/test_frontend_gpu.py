@@ -559,3 +559,51 @@ def test_frequency_major_output_layouts(FE, fast_log, pcm16):
     with pytest.raises(Exception):
         fe64.forward_packed(packed, [0], None, None, None)
     fe64.close()
+
+
+def test_batches_above_the_parameter_space_limit_go_out_in_chunks(FE):
+    """More than 128 clips without a statistics pass: several launches of <= 128 clips (descriptors as kernel parameters,
+    launches overlapping) instead of one with uploaded descriptors -- same bits as one launch and as clip-by-clip calls;
+    a validation error anywhere in the batch is reported before anything is written."""
+    fe = FE(CONF)
+    waves = [synth_wave(1200 + i, n) for i, n in enumerate((160000, 120000, 160000, 52000, 16000))]
+    from psla_b200.frontend import pack_waveforms
+    packed = pack_waveforms(waves, device=fe.device)
+    B = 300  # 3 chunks of 100
+    src1 = [b % 5 for b in range(B)]
+    src2 = [{1: 0, 3: 2}.get(b % 5, -1) for b in range(B)]  # partners at least as long: no statistics
+    lam = [0.2 + 0.002 * b for b in range(B)]
+    torch.manual_seed(3)
+    masks = [O.draw_mask_offsets(48, 192, 128, 1056) for _ in range(B)]
+    n0 = fe.launch_count
+    chunked = fe.forward_packed(packed, src1, src2, lam, masks)
+    assert fe.launch_count - n0 == 3
+    fe.set_param_meta(False)  # one launch, descriptors uploaded
+    n0 = fe.launch_count
+    single = fe.forward_packed(packed, src1, src2, lam, masks)
+    assert fe.launch_count - n0 == 1
+    fe.set_param_meta(True)
+    assert torch.equal(chunked, single)
+    for b in (0, 99, 100, 101, 199, 200, 299):
+        one = fe.forward_packed(packed, [src1[b]], [src2[b]], [lam[b]], [masks[b]])
+        assert torch.equal(one[0], chunked[b])
+    ref = O.batch_torch(waves, src1[:10], src2[:10], lam[:10], masks[:10], 1056, MEAN, STD)
+    _check(chunked[:10], ref, fill=_fill())
+    # an invalid clip in the LAST chunk: error, and no chunk has been launched
+    out = torch.full((B, 1056, 128), 7.0, device=fe.device)
+    bad = list(src1)
+    bad[-1] = 99
+    n0 = fe.launch_count
+    with pytest.raises(Exception):
+        fe.forward_packed(packed, bad, src2, lam, masks, out=out)
+    torch.cuda.synchronize()
+    assert fe.launch_count == n0 and bool((out == 7.0).all())
+    # with a statistics clip in the batch (shorter partner) it stays one launch + the statistics kernel
+    src2s = list(src2)
+    src2s[7] = 4
+    n0 = fe.launch_count
+    stats = fe.forward_packed(packed, src1, src2s, lam, masks)
+    assert fe.launch_count - n0 == 2
+    keep = [b for b in range(B) if b != 7]
+    assert torch.equal(stats[keep], chunked[keep])
+    fe.close()

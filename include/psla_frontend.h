@@ -172,7 +172,7 @@ int psla_frontend_set_cost_model(psla_frontend_t* handle, int live, int dead, in
  * 0: as a copy on `stream` itself.  Results do not depend on it. */
 int psla_frontend_set_meta_stream(psla_frontend_t* handle, int enable);
 
-/* 1 (default): a forward() of at most 128 clips whose output range is disjoint from the previous forward()'s on the same stream is launched
+/* 1 (default): a forward() of at most 128 clips whose output range is disjoint from those of the previous three launches on the same stream is launched
  * with programmatic stream serialization, so its thread blocks start on SMs the previous launch has already left
  * (stream order towards every other operation is unchanged).  0: plain launches.  Results do not depend on it. */
 int psla_frontend_set_launch_overlap(psla_frontend_t* handle, int enable);

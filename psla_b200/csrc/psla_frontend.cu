@@ -85,8 +85,11 @@ struct psla_frontend {
     int pdl = 1;
     bool prev_valid = false;
     void* prev_stream = nullptr;
-    const char* prev_out_lo = nullptr;
-    const char* prev_out_hi = nullptr;
+    // output ranges of the last kPrevOuts launches: a launch may start while its predecessor runs, and -- when that
+    // predecessor's thread blocks retire early (tiny batches) -- conceivably while the one before is not done either
+    static constexpr int kPrevOuts = 3;
+    const char* prev_out_lo[kPrevOuts] = {nullptr, nullptr, nullptr};
+    const char* prev_out_hi[kPrevOuts] = {nullptr, nullptr, nullptr};
     // forward_host device buffers
     float* d_wav = nullptr;
     size_t d_wav_cap = 0;
@@ -597,12 +600,20 @@ int enqueue_batch(psla_frontend_t* h, const void* wav, bool pcm16, ClipDesc* des
     // conflict: same stream, no statistics kernel in between, disjoint output ranges, no tracing.
     const char* out_lo = reinterpret_cast<const char*>(out);
     const char* out_hi = out_lo + static_cast<size_t>(n_clips) * target_length * h->nmel * out_elem_bytes(h);
-    const bool overlap_ok = h->pdl && param_meta && !h->trace && !h->timing && h->prev_valid && h->prev_stream == stream_ &&
-                            (out_hi <= h->prev_out_lo || out_lo >= h->prev_out_hi);
+    bool disjoint = true;
+    for (int i = 0; i < psla_frontend::kPrevOuts; ++i)
+        disjoint = disjoint && (!h->prev_out_lo[i] || out_hi <= h->prev_out_lo[i] || out_lo >= h->prev_out_hi[i]);
+    const bool overlap_ok = h->pdl && param_meta && !h->trace && !h->timing && h->prev_valid && h->prev_stream == stream_ && disjoint;
+    if (h->prev_stream != stream_)  // ranges written on another stream are ordered by the caller, not by us
+        for (int i = 0; i < psla_frontend::kPrevOuts; ++i) h->prev_out_lo[i] = h->prev_out_hi[i] = nullptr;
     h->prev_valid = true;
     h->prev_stream = stream_;
-    h->prev_out_lo = out_lo;
-    h->prev_out_hi = out_hi;
+    for (int i = psla_frontend::kPrevOuts - 1; i > 0; --i) {
+        h->prev_out_lo[i] = h->prev_out_lo[i - 1];
+        h->prev_out_hi[i] = h->prev_out_hi[i - 1];
+    }
+    h->prev_out_lo[0] = out_lo;
+    h->prev_out_hi[0] = out_hi;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((h->num_sms > 0 ? h->num_sms : 148) * kCtasPerSm);
     cfg.blockDim = dim3(kThreads);

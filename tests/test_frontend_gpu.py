@@ -306,6 +306,17 @@ def test_launch_plumbing_does_not_change_results(fe):
             fe.forward_packed(*args, out=outs[3], target_length=200)  # same buffer twice in a row: no overlap allowed
         torch.cuda.synchronize()
         assert all(torch.equal(o.cpu(), ref) for o in outs)
+        # two buffers used alternately by tiny batches of DIFFERENT clips: the last writer of each buffer must win (a launch
+        # may overlap its predecessor, never an earlier writer of the same range)
+        singles = [fe.forward_packed(packed, s1[i:i + 1], None, None, None, target_length=200).cpu() for i in range(6)]
+        bufs = [torch.empty(1, 200, 128, device=fe.device) for _ in range(2)]
+        last = [None, None]
+        for k in range(60):
+            i = (k * 5 + k // 7) % 6
+            fe.forward_packed(packed, s1[i:i + 1], None, None, None, out=bufs[k % 2], target_length=200)
+            last[k % 2] = i
+        torch.cuda.synchronize()
+        assert torch.equal(bufs[0].cpu(), singles[last[0]]) and torch.equal(bufs[1].cpu(), singles[last[1]])
         fe.set_cost_model(32, 1, 0)
         assert torch.equal(fe.forward_packed(*args, target_length=200).cpu(), ref)
     finally:

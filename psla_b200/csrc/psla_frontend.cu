@@ -490,10 +490,10 @@ int enqueue_batch(psla_frontend_t* h, const void* wav, bool pcm16, ClipDesc* des
     const bool small = n_clips <= kParamClips;
     const int G = (target_length + kGroupFrames - 1) / kGroupFrames;
     // ---- enqueue ----
-    // Small batches without a statistics pass read their descriptors from the kernel's parameter space: nothing is
-    // uploaded and nothing sits between two launches on the stream.  Otherwise: pinned slot -> device slot of the
-    // workspace on the copy stream, the kernel ordered after it by an event.
-    const bool param_meta = small && !any_stats && h->param_meta;
+    // Small batches read their descriptors from the kernels' parameter space (the statistics kernel's too): nothing is
+    // uploaded and, without a statistics pass, nothing sits between two launches on the stream.  Otherwise: pinned slot
+    // -> device slot of the workspace on the copy stream, the kernels ordered after it by an event.
+    const bool param_meta = small && h->param_meta;
     ClipDesc* d_desc = nullptr;
     ClipCost* d_cost = nullptr;
     double* d_part = reinterpret_cast<double*>(static_cast<char*>(workspace) + kMetaSlots * meta_bytes);
@@ -534,8 +534,15 @@ int enqueue_batch(psla_frontend_t* h, const void* wav, bool pcm16, ClipDesc* des
         PSLA_CUDA(h, cudaEventRecord(ev.e[0], stream));
     }
     if (any_stats) {
-        if (pcm16) clip_stats_kernel<short><<<dim3(kStatSegs, n_clips), 256, 0, stream>>>(static_cast<const short*>(wav), d_desc, d_part);
-        else clip_stats_kernel<float><<<dim3(kStatSegs, n_clips), 256, 0, stream>>>(static_cast<const float*>(wav), d_desc, d_part);
+        const dim3 sg(kStatSegs, n_clips);
+        const MetaNone none = {0};
+        if (param_meta) {
+            if (pcm16) clip_stats_kernel<short, true><<<sg, 256, 0, stream>>>(static_cast<const short*>(wav), nullptr, h->meta_host, d_part);
+            else clip_stats_kernel<float, true><<<sg, 256, 0, stream>>>(static_cast<const float*>(wav), nullptr, h->meta_host, d_part);
+        } else {
+            if (pcm16) clip_stats_kernel<short, false><<<sg, 256, 0, stream>>>(static_cast<const short*>(wav), d_desc, none, d_part);
+            else clip_stats_kernel<float, false><<<sg, 256, 0, stream>>>(static_cast<const float*>(wav), d_desc, none, d_part);
+        }
         PSLA_CUDA(h, cudaGetLastError());
         h->launches += 1;
     }
@@ -603,7 +610,9 @@ int enqueue_batch(psla_frontend_t* h, const void* wav, bool pcm16, ClipDesc* des
     bool disjoint = true;
     for (int i = 0; i < psla_frontend::kPrevOuts; ++i)
         disjoint = disjoint && (!h->prev_out_lo[i] || out_hi <= h->prev_out_lo[i] || out_lo >= h->prev_out_hi[i]);
-    const bool overlap_ok = h->pdl && param_meta && !h->trace && !h->timing && h->prev_valid && h->prev_stream == stream_ && disjoint;
+    // (never after a statistics kernel: this kernel does not wait on its predecessor, so it must not be released early
+    // behind the kernel whose sums it reads)
+    const bool overlap_ok = h->pdl && param_meta && !any_stats && !h->trace && !h->timing && h->prev_valid && h->prev_stream == stream_ && disjoint;
     if (h->prev_stream != stream_)  // ranges written on another stream are ordered by the caller, not by us
         for (int i = 0; i < psla_frontend::kPrevOuts; ++i) h->prev_out_lo[i] = h->prev_out_hi[i] = nullptr;
     h->prev_valid = true;

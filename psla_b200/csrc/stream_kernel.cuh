@@ -204,11 +204,15 @@ __device__ __forceinline__ float strided_sum(const S* __restrict__ w, int lo, in
 // audioset_dataset.py:92 / :98-99 / :117.  grid = (kStatSegs, B), block = 256.  Deterministic: fixed partition, fixed
 // reduction tree; the streaming kernel adds the kStatSegs partials in a fixed order.
 // ------------------------------------------------------------------------------------------------
-template <class S>
+// PMETA: the descriptors come in the kernel's parameter space (batches of <= kParamClips clips: nothing is uploaded).
+template <class S, bool PMETA>
 __global__ void __launch_bounds__(256) clip_stats_kernel(const S* __restrict__ wav, const ClipDesc* __restrict__ desc,
+                                                         const __grid_constant__ std::conditional_t<PMETA, MetaBlock, MetaNone> meta,
                                                          double* __restrict__ partials) {
     const int b = blockIdx.y, g = blockIdx.x, tid = threadIdx.x;
-    const ClipDesc d = load_desc(desc + b);
+    ClipDesc d;
+    if constexpr (PMETA) d = meta.desc[b];
+    else d = load_desc(desc + b);
     if (!(d.flags & kFlagStats)) return;
     float s1, s2 = 0.f, s2c = 0.f;
     {

@@ -537,11 +537,11 @@ int enqueue_batch(psla_frontend_t* h, const void* wav, bool pcm16, ClipDesc* des
         const dim3 sg(kStatSegs, n_clips);
         const MetaNone none = {0};
         if (param_meta) {
-            if (pcm16) clip_stats_kernel<short, true><<<sg, 256, 0, stream>>>(static_cast<const short*>(wav), nullptr, h->meta_host, d_part);
-            else clip_stats_kernel<float, true><<<sg, 256, 0, stream>>>(static_cast<const float*>(wav), nullptr, h->meta_host, d_part);
+            if (pcm16) clip_stats_kernel<short, true><<<sg, 256, 0, stream>>>(static_cast<const short*>(wav), nullptr, h->meta_host, d_part, h->exact_mean);
+            else clip_stats_kernel<float, true><<<sg, 256, 0, stream>>>(static_cast<const float*>(wav), nullptr, h->meta_host, d_part, h->exact_mean);
         } else {
-            if (pcm16) clip_stats_kernel<short, false><<<sg, 256, 0, stream>>>(static_cast<const short*>(wav), d_desc, none, d_part);
-            else clip_stats_kernel<float, false><<<sg, 256, 0, stream>>>(static_cast<const float*>(wav), d_desc, none, d_part);
+            if (pcm16) clip_stats_kernel<short, false><<<sg, 256, 0, stream>>>(static_cast<const short*>(wav), d_desc, none, d_part, h->exact_mean);
+            else clip_stats_kernel<float, false><<<sg, 256, 0, stream>>>(static_cast<const float*>(wav), d_desc, none, d_part, h->exact_mean);
         }
         PSLA_CUDA(h, cudaGetLastError());
         h->launches += 1;

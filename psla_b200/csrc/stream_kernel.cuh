@@ -208,14 +208,15 @@ __device__ __forceinline__ float strided_sum(const S* __restrict__ w, int lo, in
 template <class S, bool PMETA>
 __global__ void __launch_bounds__(256) clip_stats_kernel(const S* __restrict__ wav, const ClipDesc* __restrict__ desc,
                                                          const __grid_constant__ std::conditional_t<PMETA, MetaBlock, MetaNone> meta,
-                                                         double* __restrict__ partials) {
+                                                         double* __restrict__ partials, int exact) {
     const int b = blockIdx.y, g = blockIdx.x, tid = threadIdx.x;
     ClipDesc d;
     if constexpr (PMETA) d = meta.desc[b];
     else d = load_desc(desc + b);
     if (!(d.flags & kFlagStats)) return;
-    float s1, s2 = 0.f, s2c = 0.f;
-    {
+    // exact == 0 (default clip-mean mode): only the partner's mean is used (enter_clip), the primary waveform is not read
+    float s1 = 0.f, s2 = 0.f, s2c = 0.f;
+    if (exact) {
         const int seg = ((d.n1 + 4 * kStatSegs - 1) / (4 * kStatSegs)) * 4;
         const int lo = min(d.n1, g * seg), hi = min(d.n1, lo + seg);
         s1 = strided_sum(wav + d.off1, lo, hi, tid, d.flags & kFlagAligned1);
@@ -226,8 +227,10 @@ __global__ void __launch_bounds__(256) clip_stats_kernel(const S* __restrict__ w
         const int lo = min(d.n2, g * seg), hi = min(d.n2, lo + seg);
         const bool al = (d.flags & kFlagAligned2) != 0;
         s2 = strided_sum(wav + d.off2, lo, hi, tid, al);
-        if (nmin >= hi) s2c = s2;                                               // segment entirely kept
-        else if (nmin > lo) s2c = strided_sum(wav + d.off2, lo, nmin, tid, al);  // the one straddling segment
+        if (exact) {
+            if (nmin >= hi) s2c = s2;                                               // segment entirely kept
+            else if (nmin > lo) s2c = strided_sum(wav + d.off2, lo, nmin, tid, al);  // the one straddling segment
+        }
     }
     __shared__ double red[8][kStatVals];
     double v0 = s1, v1 = s2, v2 = s2c;

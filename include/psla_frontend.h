@@ -172,10 +172,28 @@ int psla_frontend_set_cost_model(psla_frontend_t* handle, int live, int dead, in
  * 0: as a copy on `stream` itself.  Results do not depend on it. */
 int psla_frontend_set_meta_stream(psla_frontend_t* handle, int enable);
 
-/* 1 (default): a forward() of at most 128 clips whose output range is disjoint from those of the previous three launches on the same stream is launched
- * with programmatic stream serialization, so its thread blocks start on SMs the previous launch has already left
- * (stream order towards every other operation is unchanged).  0: plain launches.  Results do not depend on it. */
-int psla_frontend_set_launch_overlap(psla_frontend_t* handle, int enable);
+/* Overlap of consecutive launches of the streaming kernel (programmatic dependent launch).  The kernel signals at its
+ * start that the next kernel on the stream may begin, and joins its predecessor before it exits.  A launch made with
+ * programmatic stream serialization therefore starts its thread blocks on SM resources the previous launch has already
+ * left (the tail of one batch overlaps the head of the next), yet never COMPLETES before that launch: whatever follows
+ * on the stream (a model step, a copy, an event) still sees both finished, and at most two launches are in flight.
+ * The kernel does NOT wait before reading its inputs, so the library attaches the attribute only behind a launch it
+ * knows to be its own:
+ *   PSLA_OVERLAP_OFF     never.
+ *   PSLA_OVERLAP_CALL    (default) between the launches of ONE forward() call: a batch of more than 128 clips goes out as
+ *                        chunks of at most 128 clips, and chunk k + 1 overlaps chunk k.  Needs nothing from the caller.
+ *   PSLA_OVERLAP_STREAM  also between consecutive forward() calls of this handle on the same stream.  CALLER CONTRACT: any
+ *                        work enqueued on that stream between two such calls must not itself release its dependents
+ *                        early (griddepcontrol.launch_dependents / cudaTriggerProgrammaticLaunchCompletion) before it
+ *                        has written this call's inputs -- some library GEMMs do.  Plain kernels, copies, memsets and
+ *                        event waits in between are fine: the launch simply waits for them in full (no overlap then).
+ * In every mode a launch only overlaps when it is at most 128 clips with its descriptors in parameter space (see
+ * psla_frontend_set_param_meta), needs no statistics pass, and writes an output range disjoint from those of the
+ * previous three launches of the handle; otherwise it is a plain launch.  Results do not depend on the mode. */
+#define PSLA_OVERLAP_OFF 0
+#define PSLA_OVERLAP_CALL 1
+#define PSLA_OVERLAP_STREAM 2
+int psla_frontend_set_launch_overlap(psla_frontend_t* handle, int mode);
 
 /* 1 (default): batches of at most 128 clips that need no statistics pass carry their clip descriptors in the kernel's
  * parameter space (no upload; required for the launch overlap above), and larger batches that need no statistics pass

@@ -6,7 +6,10 @@ import shutil
 import subprocess
 
 CSRC = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc")
-LIB = os.path.join(CSRC, "libpsla_frontend.so")
+# PSLA_FRONTEND_LIB: load another build of the same sources (kernel experiments, scripts/build_variants.py)
+BUILT_LIB = os.path.join(CSRC, "libpsla_frontend.so")
+LIB = os.environ.get("PSLA_FRONTEND_LIB") or BUILT_LIB
+VARIANT_DIR = os.path.join(CSRC, "variants")
 SOURCES = ("psla_frontend.cu", "tables.cc")
 HEADERS = ("fft_core.cuh", "fbank_stream.cuh", "stream_kernel.cuh", "noise_roll.cuh", "tables.h", os.path.join("..", "..", "include", "psla_frontend.h"))
 NVCC_FLAGS = ("-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -21,27 +24,43 @@ def _nvcc() -> str:
 
 
 def is_stale() -> bool:
-    if not os.path.exists(LIB):
+    if not os.path.exists(BUILT_LIB):
         return True
-    t = os.path.getmtime(LIB)
+    t = os.path.getmtime(BUILT_LIB)
     return any(os.path.getmtime(os.path.join(CSRC, f)) > t for f in SOURCES + HEADERS)
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
     """Compile the CUDA library if missing or older than its sources; returns its path."""
     if not force and not is_stale():
-        return LIB
-    cmd = [_nvcc(), *NVCC_FLAGS, "-o", LIB + ".tmp", *SOURCES]
+        return BUILT_LIB
+    cmd = [_nvcc(), *NVCC_FLAGS, "-o", BUILT_LIB + ".tmp", *SOURCES]
     if verbose:
         cmd.insert(1, "-Xptxas")
         cmd.insert(2, "-v")
     res = subprocess.run(cmd, cwd=CSRC, capture_output=True, text=True)
     if res.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
-    os.replace(LIB + ".tmp", LIB)
+    os.replace(BUILT_LIB + ".tmp", BUILT_LIB)
     if verbose:
         print(res.stderr)
-    return LIB
+    return BUILT_LIB
+
+
+def build_variant(name: str, defines=(), slim: bool = True, verbose: bool = False) -> str:
+    """Experimental build csrc/variants/libpsla_<name>.so with extra -D flags.  slim: only the kernels the bench batch uses
+    (-DPSLA_SLIM: default clip-mean mode, 128 mel bins, fp32 samples, [B, T, F] output) -- seconds instead of minutes."""
+    os.makedirs(VARIANT_DIR, exist_ok=True)
+    out = os.path.join(VARIANT_DIR, f"libpsla_{name}.so")
+    cmd = [_nvcc(), *NVCC_FLAGS, *(["-DPSLA_SLIM"] if slim else []), *[f"-D{d}" for d in defines], "-Xptxas", "-v", "-o", out, *SOURCES]
+    res = subprocess.run(cmd, cwd=CSRC, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError(f"nvcc failed for variant {name}:\n" + res.stdout + res.stderr)
+    if verbose:
+        print(res.stderr)
+    with open(out + ".ptxas.txt", "w") as f:
+        f.write(res.stderr)
+    return out
 
 
 if __name__ == "__main__":

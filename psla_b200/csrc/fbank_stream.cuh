@@ -5,15 +5,15 @@
 // torchaudio/compliance/kaldi.py:138-140 as called at src/dataloaders/audioset_dataset.py:119-120).
 //
 // Work unit of a WARP: a GROUP of 4 consecutive frames of one clip = 880 staged samples.  A warp walks along a
-// clip group by group; the 240 samples two consecutive groups share stay in its private shared-memory window,
-// only 640 new samples are staged per step.  No CTA-level barrier exists after the table load.
+// clip group by group; the 240 samples two consecutive groups share stay where they are in its private shared-memory
+// window (two overlap buffers used alternately), only 640 new samples are staged per step.  No CTA-level barrier exists after the table load.
 //
 // Inside a group each HALF-WARP turns a frame pair (x, y) into ONE 512-point complex FFT of z = x + i*y
 // (32 complex values = 64 registers per lane):
 //   pass 1   lane n2 (0..15) holds z[16*n1 + n2], n1 = 0..31 (only n1 < 25 is non-zero: 400 = 25*16).  The y frame
 //            starts 160 samples = 10 n1-steps after the x frame, so ONE run of 35 staged values feeds both.
 //            -> 32-point DIT FFT over n1 in registers (FMA-only butterflies, first stage pruned for the 7 zero inputs) -> shared memory
-//            EX[k1][n2], untwiddled (row 0 pre-multiplied by W_32^-n2, see below).  EX aliases the staged samples (kWsEX).
+//            EX[k1][n2], untwiddled (row 0 pre-multiplied by W_32^-n2, see below).  EX aliases the middle of the staged samples (kWsEX).
 //   pass 2   lane t reads rows ka = t and kb = 32 - t (lane 0: rows 0 and 16; pass 1 stored them side by side), multiplies row ka by
 //            TW[t][n2] = W_512^(t*n2) and row kb by conj(TW[t][n2]): because W_512^((32-t)*n2) = W_16^n2 * conj(TW[t][n2])
 //            and a modulation by W_16^n2 only rotates the 16-point FFT's output index by one, both rows share one
@@ -84,12 +84,20 @@ constexpr int kGroupSamples = (kGroupFrames - 1) * kFrameShift + kFrameLen;     
 constexpr int kStepSamples = kGroupFrames * kFrameShift;                         // 640 new samples per step
 constexpr int kOverlapSamples = kGroupSamples - kStepSamples;                    // 240
 
-// Staged-sample layout of a warp's window: 16 floats of padding after every 320 samples so that the two half-warps
-// (whose frame pairs start 320 samples apart, i.e. on the same bank) read disjoint bank halves.
-PSLA_HDC int dpad(int u) { return u + 16 * (u / 320); }
-constexpr int kDFloats = 912;  // dpad(879) + 1
-constexpr int kBsFloats = 56;  // 55 sums of 16 samples
-constexpr int kXsFloats = 8;   // (1-p) * x at u = 0, 160, ..., 800
+// Staged-sample layout of a warp's window.  A group's 880 samples live in three pieces, so that the 240 samples two
+// consecutive groups share never have to be moved:
+//   OV[par]      window samples [0, 240)    -- written by the PREVIOUS group's staging (or a cold start)
+//   DM           window samples [240, 640)  -- with 16 floats of padding at sample 320
+//   OV[par ^ 1]  window samples [640, 880)  -- the next group's [0, 240)
+// par = group index & 1.  Bank rule (pass 1 reads, per instruction, sample u in half-warp 0 and u + 320 in half-warp 1):
+// both OV buffers start on bank 0, DM on bank 16, and the padding at 320 keeps the two half-warps on disjoint bank halves.
+constexpr int kOvFloats = 256;  // >= kOverlapSamples, multiple of 32
+// physical float offset inside the warp window of window sample u (see kWsOV / kWsDM below)
+PSLA_HDC int wpos(int u, int par) {
+    return u < 240 ? par * kOvFloats + u : (u < 640 ? 2 * kOvFloats + 16 + (u - 240) + (u >= 320 ? 16 : 0) : (par ^ 1) * kOvFloats + (u - 640));
+}
+constexpr int kBsFloats = 56;  // 55 sums of 16 samples (one such array per parity: sums 40..54 are also the next group's 0..14)
+constexpr int kXsFloats = 8;   // (1-p) * x at u = 0, 160, 320, 480 (per parity; u = 640, 800 are the next group's 0, 160)
 // Exchange buffer of one frame pair, organised by the ROW PAIRS pass 2 consumes: EX[t][n2] = (Z1[ka][n2], Z1[kb][n2]) with
 // ka = t, kb = 32 - t (t = 0: rows 0 and 16) -- 16 bytes per (t, n2), so pass 1 stores and pass 2 loads are all 128-bit.
 // Row stride 68 floats: the 8 lanes of a quarter-warp (4 consecutive t x 2 pairs) read 8 distinct 16-byte bank groups.
@@ -104,19 +112,22 @@ constexpr int kExFloats = kExSecondPair + kExPairFloats;  // 2192
 constexpr int kPFloats = 4 * (kNfft / 2);  // bins 0..255 (bin 256 never carries mel weight: kaldi.py:627 pads a zero column)
 static_assert(kPFloats <= kExFloats, "P must fit in the warp's exchange buffers");
 
-// per-warp shared-memory window (floats).  The exchange buffers ALIAS the staged samples from sample 256 on: once every
-// lane of the warp holds its pass-1 inputs in registers and the 240 samples shared with the next group have moved to
-// the front (stage_shift), the rest of D is dead until the next step commits its new samples -- by then the power
-// spectra (which alias EX) have been consumed by the mel stage.  10.2 KB per warp instead of 13.3 KB: four CTAs of 4
-// warps (each with its own copy of the tables) fit one SM, so a following launch takes over SM resources in small steps.
-constexpr int kWsD = 0;
-constexpr int kWsEX = 256;  // >= kOverlapSamples (the part of D that survives the shift), multiple of 32 (same banks)
-constexpr int kWsBS = kWsEX + kExFloats;
-constexpr int kWsXS = kWsBS + kBsFloats;
-constexpr int kWsCS = kWsXS + kXsFloats;  // per-clip state of the warp (kept out of the register file, see stream_kernel.cuh)
+// per-warp shared-memory window (floats).  The exchange buffers ALIAS the middle piece DM of the staged samples: once
+// every lane of the warp holds its pass-1 inputs in registers DM is dead until the next step commits its new samples --
+// by then the power spectra (which alias EX) have been consumed by the mel stage.  The two overlap buffers sit below
+// EX and survive.  11.2 KB per warp: four CTAs of 4 warps (each with its own copy of the tables) fit one SM, so a
+// following launch takes over SM resources in small steps.
+constexpr int kWsOV = 0;                      // OV[0], OV[1]
+constexpr int kWsEX = 2 * kOvFloats;          // 512: multiple of 32
+constexpr int kWsDM = kWsEX + 16;             // bank 16 (see above); inside EX
+constexpr int kDmFloats = 400 + 16;
+constexpr int kWsBS = kWsEX + kExFloats;      // BS[0], BS[1]
+constexpr int kWsXS = kWsBS + 2 * kBsFloats;  // XS[0], XS[1]
+constexpr int kWsCS = kWsXS + 2 * kXsFloats;  // per-clip state of the warp (kept out of the register file, see stream_kernel.cuh)
 constexpr int kCsWords = 36;
-constexpr int kWarpFloats = kWsCS + kCsWords;  // 2676 floats = 10704 B
-static_assert(kWsEX >= kOverlapSamples && kWsEX % 32 == 0 && kWsEX + kExFloats >= kDFloats, "EX aliases the tail of D");
+constexpr int kWarpFloats = kWsCS + kCsWords;  // 2868 floats = 11472 B
+static_assert(kOvFloats >= kOverlapSamples && kWsEX % 32 == 0 && kWsDM % 32 == 16 && kDmFloats + 16 <= kExFloats, "EX aliases DM only");
+static_assert(wpos(0, 0) == kWsOV && wpos(240, 0) == kWsDM && wpos(240, 1) == kWsDM && wpos(640, 0) == kOvFloats && wpos(640, 1) == 0, "window pieces");
 static_assert((kWsEX * 4) % 16 == 0 && (kWsCS * 4) % 16 == 0 && (kWarpFloats * 4) % 16 == 0, "16-byte alignment of vector regions");
 
 // Constant tables (floats), copied once per CTA into shared memory.
@@ -137,28 +148,40 @@ constexpr int kMelSpec0 = 2, kMelSpec1 = 3, kMelSpec2 = 6, kMelSpec3 = 10;
 
 // ---------------------------------------------------------------------------------------------
 // Pass 1 of half-warp h, lane n2: frames 2h (x) and 2h+1 (y) of the group.
-//   D     staged d[u] = x[u] - p*x[u-1] in dpad() layout,  XS[f] = (1-p) * x[160 f]
+//   WS    the warp window: staged d[u] = x[u] - p*x[u-1] at wpos(u, par),  XS[par][f] = (1-p) * x[160 f]
 //   cmu_* per-frame means pre-multiplied by (1-p): per-frame DC removal (kaldi.py:183-186) and pre-emphasis
 //         (:193-198) commute into  d[j] - (1-p)*mu  (first sample: (1-p)*(x0 - mu), replicate padding)
 // ---------------------------------------------------------------------------------------------
-PSLA_HD void pair_pass1(int n2, int h, const float* __restrict__ D, const float* __restrict__ XS,
-                        const float* __restrict__ WINT, float cmu_x, float cmu_y, cf (&z)[32]) {
+PSLA_HD void pair_pass1(int n2, int h, int par, const float* __restrict__ WS, const float* __restrict__ WINT, float cmu_x, float cmu_y,
+                        cf (&z)[32]) {
     {
-        // element n1 of the run sits at dx[16*n1 + (n1 >= 20 ? 16 : 0)]; x frame: n1 = 0..24, y frame: n1 = 10..34
-        const float* dx = D + 336 * h + n2;
+        // element n1 of the lane's run is window sample u = 320 h + 16 n1 + n2; x frame: n1 = 0..24, y frame: n1 = 10..34.
+        // The run crosses the window pieces at fixed n1 (15: u = 240, 20: u = 320 / 640), so three base pointers with
+        // the piece offsets folded in make every load an immediate offset: v[n1] = p(n1)[16 n1].
+        const float* ovp = WS + kWsOV + par * kOvFloats;
+        const float* ovo = WS + kWsOV + (par ^ 1) * kOvFloats;
+        const float* dm = WS + kWsDM;
+        const float* pa = (h == 0 ? ovp : dm + 96) + n2;        // n1 < 15   h = 0: u < 240   h = 1: DM (u >= 320: + 16 padding)
+        const float* pb = (h == 0 ? dm - 240 : dm + 96) + n2;   // n1 < 20   h = 0: 240 <= u < 320
+        const float* pc = (h == 0 ? dm - 224 : ovo - 320) + n2;  // n1 >= 20  h = 0: u >= 320 (+ 16)   h = 1: u >= 640
+        const float* XS = WS + kWsXS + par * kXsFloats;
         // replicate-padded first samples: lane 0 reads (1-p)*x0 from XS instead of d[0]; an address select, so that
         // lane 0 does not get a code path of its own
-        const float* x0p = (n2 == 0) ? XS + 2 * h : dx;
-        const float* y0p = (n2 == 0) ? XS + 2 * h + 1 : dx + 160;
+        const float* x0p = (n2 == 0) ? XS + 2 * h : pa;
+        const float* y0p = (n2 == 0) ? XS + 2 * h + 1 : pa + 160;
         float w[kWinRow];
         static_for<0, kWinRow / 4>([&](auto q_) {
             constexpr int q = decltype(q_)::value;
+#ifdef PSLA_X_NOWIN  // what-if timing build (wrong results): no window loads
+            w[4 * q] = w[4 * q + 1] = w[4 * q + 2] = w[4 * q + 3] = 0.5f;
+#else
             ld4(WINT + kWinRow * n2 + 4 * q, w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+#endif
         });
         float v[35];
         static_for<0, 35>([&](auto n1_) {
             constexpr int n1 = decltype(n1_)::value;
-            v[n1] = (n1 == 0) ? x0p[0] : dx[16 * n1 + (n1 >= 20 ? 16 : 0)];
+            v[n1] = (n1 == 0) ? x0p[0] : (n1 < 15 ? pa : (n1 < 20 ? pb : pc))[16 * n1];
         });
         const float vy0 = y0p[0];
         static_for<0, 25>([&](auto n1_) {
@@ -169,8 +192,8 @@ PSLA_HD void pair_pass1(int n2, int h, const float* __restrict__ D, const float*
     }
     fft_dit<32, 5, 25>(z);  // inputs n1 >= 25 are zero (400 = 25 * 16)
 }
-// The stores of pass 1, separate because EX aliases D: every lane of the warp must have read its samples (and the
-// overlap must have been shifted) before any lane stores (__syncwarp on the device, loop order on the host).
+// The stores of pass 1, separate because EX aliases DM: every lane of the warp must have read its samples before any
+// lane stores (__syncwarp on the device, loop order on the host).
 PSLA_HD void pair_pass1_store(int n2, const float* __restrict__ TWZ, float* __restrict__ EX, const cf (&z)[32]) {
     float zr, zi;
     ld2(TWZ + 2 * n2, zr, zi);
@@ -199,7 +222,11 @@ PSLA_HD void pair_pass2_fft(int t, const float* __restrict__ EX, const float* __
     static_for<0, 8>([&](auto q_) {
         constexpr int n = 2 * decltype(q_)::value;
         float w0r, w0i, w1r, w1i;
+#ifdef PSLA_X_NOTW  // what-if timing build (wrong results): no twiddle loads
+        w0r = 0.6f, w0i = 0.8f, w1r = 0.8f, w1i = -0.6f;
+#else
         ld4(tw + 2 * n, w0r, w0i, w1r, w1i);
+#endif
         if constexpr (n != 0) {  // TW[t][0] == 1
             a[n] = cmul(a[n], w0r, w0i);
             b[n] = cmul_conj(b[n], w0r, w0i);
@@ -231,6 +258,10 @@ PSLA_HD void pair_power_store(int t, int h, const cf (&a)[16], const cf (&b)[16]
         constexpr int ia = brev<4>(k2);              // A[k2]
         constexpr int ib = brev<4>((16 - k2) % 16);  // B[(16-k2) % 16]
         cf u, v;
+#ifdef PSLA_X_NOSEL  // what-if timing build (wrong results in lanes 0, 1): no lane-0 selects
+        u = a[ia];
+        v = b[ib];
+#else
         if constexpr (k2 < 8) {
             u = a[ia];
             constexpr int ia2 = brev<4>((16 - k2) % 16);  // lane 0: A[(16-k2) % 16]
@@ -242,6 +273,7 @@ PSLA_HD void pair_power_store(int t, int h, const cf (&a)[16], const cf (&b)[16]
             u.y = t0 ? b[ib2].y : a[ia].y;
             v = b[ib];
         }
+#endif
         const cf x = cadd(u, conj_(v));  // X = u + conj(v)
         const cf y = csub(u, conj_(v));  // i*Y = u - conj(v)
         const float px = fmaf(x.x, x.x, x.y * x.y);
@@ -266,9 +298,17 @@ template <int R, int OFF>
 PSLA_HD void mel_slot_static(int lane, const float* __restrict__ P, const float* __restrict__ w, int start, float (&acc)[kGroupFrames]) {
     cf a01 = mk(0.f, 0.f), a23 = mk(0.f, 0.f);  // frames (0, 1) and (2, 3): one two-wide FMA each per tap
     const float* p = P + 4 * start;
+#ifdef PSLA_X_MELHALF  // what-if timing build (wrong results): half the taps
+    static_for<0, (R + 1) / 2>([&](auto r_) {
+#else
     static_for<0, R>([&](auto r_) {
+#endif
         constexpr int r = decltype(r_)::value;
+#ifdef PSLA_X_NOMELW  // what-if timing build (wrong results): no weight loads
+        const float wv = 0.25f;
+#else
         const float wv = w[32 * (OFF + r) + lane];
+#endif
         cf p01, p23;
         ld4(p + 4 * r, p01.x, p01.y, p23.x, p23.y);
         a01 = cfma(p01, bc(wv), a01);

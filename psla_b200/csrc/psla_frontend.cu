@@ -36,7 +36,8 @@
 using namespace psla;
 
 constexpr int kMetaSlots = 4;
-constexpr int kCtasPerSm = 4;  // __launch_bounds__(kThreads, 4): 4 warps x 128 registers and ~51 KB of shared memory per CTA
+constexpr int kCtasPerSm = 4;  // __launch_bounds__(kThreads, 4): 4 warps x 128 registers and ~53 KB of shared memory per CTA
+constexpr size_t kSmemPerSm = 228 * 1024, kSmemPerCtaReserved = 1024, kSmemPerCtaMax = 227 * 1024;
 
 struct psla_frontend {
     int device = 0;
@@ -49,6 +50,7 @@ struct psla_frontend {
     float* d_tab = nullptr;
     int tab_floats = 0;
     size_t smem_bytes = 0;
+    int ctas_per_sm = kCtasPerSm;  // resident CTAs per SM the shared-memory footprint allows (4 with the 128-bin tables)
     int fast_log = 0;
     float lg2_eps = -23.0f;  // what the device's lg2.approx returns for the float epsilon (probed once in create())
     int exact_mean = 0;
@@ -81,12 +83,14 @@ struct psla_frontend {
     std::vector<ClipDesc> big_descs;
     std::vector<ClipCost> big_costs;
     int param_meta = 1;
-    // programmatic overlap of consecutive launches (psla_frontend_set_launch_overlap)
-    int pdl = 1;
+    // programmatic overlap of consecutive launches (psla_frontend_set_launch_overlap): 0 never, 1 between the launches of
+    // ONE forward() call (default: the library itself enqueued the predecessor), 2 also across forward() calls (caller contract)
+    int pdl = PSLA_OVERLAP_CALL;
     bool prev_valid = false;
     void* prev_stream = nullptr;
-    // output ranges of the last kPrevOuts launches: a launch may start while its predecessor runs, and -- when that
-    // predecessor's thread blocks retire early (tiny batches) -- conceivably while the one before is not done either
+    // output ranges of the last kPrevOuts launches.  Every launch joins its predecessor before it exits (pdl_join in
+    // stream_kernel.cuh) and the grid fills the resident-CTA capacity, so only ADJACENT launches can be in flight
+    // together; three ranges are kept as margin for devices / carve-outs where more thread blocks are resident.
     static constexpr int kPrevOuts = 3;
     const char* prev_out_lo[kPrevOuts] = {nullptr, nullptr, nullptr};
     const char* prev_out_hi[kPrevOuts] = {nullptr, nullptr, nullptr};
@@ -142,6 +146,33 @@ cudaError_t prepare_one(size_t smem) {
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(fbank_stream_kernel<EXACT, MELSPEC, PMETA, S, TRACE, OUT>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
 }
+#ifdef PSLA_SLIM
+// Experimental builds (psla_b200/build.py build_variant): only the kernels the bench batch uses are instantiated --
+// default clip-mean mode, specialised 128-bin mel path, fp32 samples, [B, T, F] output (both descriptor paths, with and
+// without the timeline).  Everything else reports cudaErrorNotSupported.
+template <class S>
+cudaError_t launch_stream_kernel(const cudaLaunchConfig_t& cfg, bool exact, bool spec, bool pmeta, bool trace, int layout,
+                                 const StreamParams& p, const MetaBlock& mb) {
+    const MetaNone none = {0};
+    if constexpr (!std::is_same_v<S, float>) return cudaErrorNotSupported;
+    else {
+        if (exact || !spec || layout != PSLA_OUT_TF_F32) return cudaErrorNotSupported;
+        if (trace) {
+            if (pmeta) return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, true, true, float, true>, p, mb);
+            return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, true, false, float, true>, p, none);
+        }
+        if (pmeta) return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, true, true, float>, p, mb);
+        return cudaLaunchKernelEx(&cfg, fbank_stream_kernel<false, true, false, float>, p, none);
+    }
+}
+cudaError_t prepare_all(size_t smem) {
+    cudaError_t e = prepare_one<false, true, false, float, false>(smem);
+    if (e == cudaSuccess) e = prepare_one<false, true, true, float, false>(smem);
+    if (e == cudaSuccess) e = prepare_one<false, true, false, float, true>(smem);
+    if (e == cudaSuccess) e = prepare_one<false, true, true, float, true>(smem);
+    return e;
+}
+#else
 template <bool EXACT, bool MELSPEC, bool TRACE>
 cudaError_t prepare_kernel(size_t smem) {
     cudaError_t e = prepare_one<EXACT, MELSPEC, false, float, TRACE>(smem);
@@ -194,13 +225,30 @@ cudaError_t launch_stream_kernel(const cudaLaunchConfig_t& cfg, bool exact, bool
     }
 }
 
+cudaError_t prepare_all(size_t smem) {
+    cudaError_t e = prepare_kernel<false, false, false>(smem);
+    if (e == cudaSuccess) e = prepare_kernel<false, true, false>(smem);
+    if (e == cudaSuccess) e = prepare_kernel<true, false, false>(smem);
+    if (e == cudaSuccess) e = prepare_kernel<true, true, false>(smem);
+    if (e == cudaSuccess) e = prepare_kernel<false, false, true>(smem);
+    if (e == cudaSuccess) e = prepare_kernel<false, true, true>(smem);
+    if (e == cudaSuccess) e = prepare_layout<kOutFT>(smem);
+    if (e == cudaSuccess) e = prepare_layout<kOutFTbf16>(smem);
+    return e;
+}
+#endif
+
 int upload_tables(psla_frontend* h) {
     std::vector<float> buf;
     bool spec = false;
     if (!build_table_buffer(h->window.data(), h->mel_dense.data(), h->nmel, &buf, &spec)) return PSLA_E_UNSUPPORTED;
     const int total = static_cast<int>(buf.size());
     const size_t smem = (static_cast<size_t>(total) + static_cast<size_t>(kWarpsPerCta) * kWarpFloats) * sizeof(float);
-    if (kCtasPerSm * (smem + 1024) > 228 * 1024) return PSLA_E_UNSUPPORTED;  // four CTAs (tables + 4 warp windows each) must fit one SM
+    // four CTAs (tables + 4 warp windows each) fit one SM with the 128-bin tables; the larger tables of small bin counts
+    // (wide triangles: more taps per lane) run with fewer resident CTAs -- the grid is sized to what is resident
+    if (smem > kSmemPerCtaMax) return PSLA_E_UNSUPPORTED;
+    const int fit = static_cast<int>(kSmemPerSm / (smem + kSmemPerCtaReserved));
+    h->ctas_per_sm = fit < kCtasPerSm ? fit : kCtasPerSm;
     if (h->d_tab) {
         PSLA_CUDA(h, cudaDeviceSynchronize());
         cudaFree(h->d_tab);
@@ -211,14 +259,7 @@ int upload_tables(psla_frontend* h) {
     h->tab_floats = total;
     h->smem_bytes = smem;
     h->mel_spec = spec;
-    PSLA_CUDA(h, (prepare_kernel<false, false, false>(smem)));
-    PSLA_CUDA(h, (prepare_kernel<false, true, false>(smem)));
-    PSLA_CUDA(h, (prepare_kernel<true, false, false>(smem)));
-    PSLA_CUDA(h, (prepare_kernel<true, true, false>(smem)));
-    PSLA_CUDA(h, (prepare_kernel<false, false, true>(smem)));
-    PSLA_CUDA(h, (prepare_kernel<false, true, true>(smem)));
-    PSLA_CUDA(h, prepare_layout<kOutFT>(smem));
-    PSLA_CUDA(h, prepare_layout<kOutFTbf16>(smem));
+    PSLA_CUDA(h, prepare_all(smem));
     PSLA_CUDA(h, cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, h->device));
     return PSLA_OK;
 }
@@ -415,7 +456,7 @@ int psla_frontend_get_timing(psla_frontend_t* h, double* stats_ms, double* tile_
 
 int psla_frontend_set_trace(psla_frontend_t* h, int64_t* device_buf, size_t capacity_records) {
     if (!h) return PSLA_E_INVALID;
-    const size_t need = static_cast<size_t>(h->num_sms > 0 ? h->num_sms : 148) * kCtasPerSm * kWarpsPerCta;
+    const size_t need = static_cast<size_t>(psla_frontend_trace_records(h));
     if (device_buf && capacity_records < need) return PSLA_E_WORKSPACE;
     static_assert(sizeof(long long) == sizeof(int64_t), "trace word");
     h->trace = reinterpret_cast<long long*>(device_buf);
@@ -423,7 +464,7 @@ int psla_frontend_set_trace(psla_frontend_t* h, int64_t* device_buf, size_t capa
 }
 
 int psla_frontend_trace_records(const psla_frontend_t* h) {
-    return h ? (h->num_sms > 0 ? h->num_sms : 148) * kCtasPerSm * kWarpsPerCta : 0;
+    return h ? (h->num_sms > 0 ? h->num_sms : 148) * h->ctas_per_sm * kWarpsPerCta : 0;
 }
 
 int psla_frontend_trace_words(void) { return kTraceWords; }
@@ -434,9 +475,9 @@ int psla_frontend_set_meta_stream(psla_frontend_t* h, int enable) {
     return PSLA_OK;
 }
 
-int psla_frontend_set_launch_overlap(psla_frontend_t* h, int enable) {
-    if (!h) return PSLA_E_INVALID;
-    h->pdl = enable ? 1 : 0;
+int psla_frontend_set_launch_overlap(psla_frontend_t* h, int mode) {
+    if (!h || mode < PSLA_OVERLAP_OFF || mode > PSLA_OVERLAP_STREAM) return PSLA_E_INVALID;
+    h->pdl = mode;
     return PSLA_OK;
 }
 
@@ -482,7 +523,7 @@ size_t out_elem_bytes(const psla_frontend* h) { return h->layout == PSLA_OUT_FT_
 // in `descs` / `costs` (h->meta_host's arrays when n_clips <= kParamClips).
 int enqueue_batch(psla_frontend_t* h, const void* wav, bool pcm16, ClipDesc* descs, ClipCost* costs, int n_clips, long long total_cost,
                   bool any_stats, int target_length, float norm_mean, float norm_div, int skip_norm, float* out, void* workspace,
-                  void* stream_) {
+                  void* stream_, bool follows_own_launch) {
     cudaStream_t stream = static_cast<cudaStream_t>(stream_);
     const size_t desc_bytes = align_up(static_cast<size_t>(n_clips) * sizeof(ClipDesc), 256);
     const size_t cost_bytes = align_up((static_cast<size_t>(n_clips) + 1) * sizeof(ClipCost), 256);
@@ -603,16 +644,21 @@ int enqueue_batch(psla_frontend_t* h, const void* wav, bool pcm16, ClipDesc* des
     p.c1 = static_cast<float>(1.0 - static_cast<double>(h->preemph));
     p.cm = h->cm;
     p.trace = h->trace;
-    // Overlap with the previous forward() of this handle (its tail SMs start this launch's CTAs) when nothing can
-    // conflict: same stream, no statistics kernel in between, disjoint output ranges, no tracing.
+    // Programmatic stream serialization lets this launch's thread blocks start on SM resources its PREDECESSOR ON THE
+    // STREAM has already left -- if that predecessor signals early, which our streaming kernel does and plain kernels /
+    // copies do not (behind those the attribute changes nothing).  This kernel does not wait before reading its
+    // inputs, so the attribute is only attached when the predecessor is known to be one of our own launches:
+    //   follows_own_launch     the previous chunk of this same forward() call (the library enqueued it a moment ago), or
+    //   PSLA_OVERLAP_STREAM    the caller's promise that nothing that signals early itself sits between two calls.
+    // Further conditions: descriptors in parameter space (no upload in between), no statistics kernel in between (its
+    // sums are read at once), output disjoint from those of the launches that may still run, no tracing / timing.
     const char* out_lo = reinterpret_cast<const char*>(out);
     const char* out_hi = out_lo + static_cast<size_t>(n_clips) * target_length * h->nmel * out_elem_bytes(h);
     bool disjoint = true;
     for (int i = 0; i < psla_frontend::kPrevOuts; ++i)
         disjoint = disjoint && (!h->prev_out_lo[i] || out_hi <= h->prev_out_lo[i] || out_lo >= h->prev_out_hi[i]);
-    // (never after a statistics kernel: this kernel does not wait on its predecessor, so it must not be released early
-    // behind the kernel whose sums it reads)
-    const bool overlap_ok = h->pdl && param_meta && !any_stats && !h->trace && !h->timing && h->prev_valid && h->prev_stream == stream_ && disjoint;
+    const bool own_pred = h->prev_valid && h->prev_stream == stream_ && (follows_own_launch || h->pdl == PSLA_OVERLAP_STREAM);
+    const bool overlap_ok = h->pdl != PSLA_OVERLAP_OFF && own_pred && param_meta && !any_stats && !h->trace && !h->timing && disjoint;
     if (h->prev_stream != stream_)  // ranges written on another stream are ordered by the caller, not by us
         for (int i = 0; i < psla_frontend::kPrevOuts; ++i) h->prev_out_lo[i] = h->prev_out_hi[i] = nullptr;
     h->prev_valid = true;
@@ -624,7 +670,7 @@ int enqueue_batch(psla_frontend_t* h, const void* wav, bool pcm16, ClipDesc* des
     h->prev_out_lo[0] = out_lo;
     h->prev_out_hi[0] = out_hi;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((h->num_sms > 0 ? h->num_sms : 148) * kCtasPerSm);
+    cfg.gridDim = dim3((h->num_sms > 0 ? h->num_sms : 148) * h->ctas_per_sm);
     cfg.blockDim = dim3(kThreads);
     cfg.dynamicSmemBytes = h->smem_bytes;
     cfg.stream = stream;
@@ -782,13 +828,13 @@ int forward_any(psla_frontend_t* h, const void* wav, bool pcm16, const int64_t* 
             const int st = enqueue_batch(h, wav, pcm16, h->meta_host.desc, h->meta_host.cost, nc, costs[c1].cum - costs[c0].cum, false,
                                          target_length, norm_mean, norm_div, skip_norm,
                                          reinterpret_cast<float*>(reinterpret_cast<char*>(out) + static_cast<size_t>(c0) * clip_bytes), workspace,
-                                         stream_);
+                                         stream_, c > 0);
             if (st != PSLA_OK) return st;
         }
         return PSLA_OK;
     }
     return enqueue_batch(h, wav, pcm16, descs, costs, n_clips, total_cost, any_stats, target_length, norm_mean, norm_div, skip_norm, out,
-                         workspace, stream_);
+                         workspace, stream_, false);
 }
 
 int forward_host_any(psla_frontend_t* h, const void* wav_host, bool pcm16, const int64_t* wav_offset, const int64_t* wav_length, int n_wav,

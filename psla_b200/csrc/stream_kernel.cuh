@@ -164,6 +164,21 @@ struct Pcm<short> {
 
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
+// Programmatic dependent launch (PDL), the two halves every launch of the streaming kernel executes:
+//   pdl_release()  at kernel entry: the NEXT kernel on the stream, if the host launched it with programmatic stream
+//                  serialization, may start its thread blocks as soon as SM resources free up;
+//   pdl_join()     on every exit path, after the thread's last global store: wait until the grid(s) this launch was
+//                  allowed to start ahead of have completed and flushed.  A launch therefore never COMPLETES before its
+//                  predecessor -- stream order stays transitive for whatever is enqueued next (a model step, a copy, an
+//                  event) -- and because waiting thread blocks keep their SM slots, at most two consecutive launches are
+//                  ever in flight together.  When the launch was not made with the attribute both are no-ops.
+__device__ __forceinline__ void pdl_release() { asm volatile("griddepcontrol.launch_dependents;"); }
+__device__ __forceinline__ void pdl_join() {
+#ifndef PSLA_NO_PDL_WAIT
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+#endif
+}
+
 // 4 consecutive samples [i, i+4) of a waveform of n samples, zeros past the end
 template <class S>
 __device__ __forceinline__ typename Pcm<S>::reg_t load4(const S* __restrict__ w, int i, int n, bool aligned) {
@@ -388,7 +403,10 @@ __device__ __forceinline__ float4 mix4(const MixState<S>& m, const float4& a, fl
 // Warp-private staging of window samples [U0, U1) of the group window ([0, 240): the part a group shares with its
 // predecessor, only staged on a cold start; [240, 880): the 640 new samples of every step).  issue() only loads (so the
 // latency can hide behind the mel / epilogue of the previous group), commit() conditions the samples and writes
-//   D[dpad(u)] = x[u] - p*x[u-1],  BS[u/16] = sum of 16 samples,  XS[u/160] = (1-p)*x[u]  (u % 160 == 0).
+//   WS[wpos(u, par)] = x[u] - p*x[u-1],  BS[par][u/16] = sum of 16 samples,  XS[par][u/160] = (1-p)*x[u]  (u % 160 == 0),
+// where the part the NEXT group shares (u >= 640) lands in the other parity's arrays at u - 640: samples in OV[par ^ 1]
+// only (this group's pass 1 reads them there), block sums in both arrays (this group's last frame needs them too).
+// Nothing is ever moved between steps.
 // `carry` is x of the last sample staged so far (pre-emphasis neighbour of the next staged sample).
 // ------------------------------------------------------------------------------------------------
 template <int U0, int U1>
@@ -425,8 +443,16 @@ __device__ __forceinline__ void stage_issue(const MixState<S>& m, int S0, int la
 template <bool EXACT, int U0, int U1, bool FULL, class S, int NIT>
 __device__ __forceinline__ void stage_commit(const MixState<S>& m, int S0, int lane, float pe, float c1,
                                              const typename Pcm<S>::reg_t (&a)[NIT], const typename Pcm<S>::reg_t (&c)[NIT],
-                                             float* __restrict__ D, float* __restrict__ BS, float* __restrict__ XS, float& carry) {
+                                             float* __restrict__ WS, int par, float& carry) {
     using Geo = StageGeom<U0, U1>;
+    float* BSp = WS + kWsBS + par * kBsFloats;
+    float* BSo = WS + kWsBS + (par ^ 1) * kBsFloats;
+    float* XSp = WS + kWsXS + par * kXsFloats;
+    float* XSo = WS + kWsXS + (par ^ 1) * kXsFloats;
+    // piece bases with the piece's first window sample folded in: sample u of the piece sits at base[u]
+    float* p_lo = WS + kWsOV + par * kOvFloats;                // u < 240
+    float* p_mid = WS + kWsDM - kOverlapSamples;               // 240 <= u < 640 (+ 16 from u = 320 on)
+    float* p_hi = WS + kWsOV + (par ^ 1) * kOvFloats - kStepSamples;  // u >= 640
     float last_w = 0.f;
 #pragma unroll
     for (int it = 0; it < Geo::kIters; ++it) {
@@ -441,36 +467,40 @@ __device__ __forceinline__ void stage_commit(const MixState<S>& m, int S0, int l
         carry = __shfl_sync(0xffffffffu, x.w, 31);
         last_w = x.w;
         float s4 = (x.x + x.y) + (x.z + x.w);
+#ifndef PSLA_X_NOBS  // what-if timing build (wrong results): block sums not reduced
         s4 += __shfl_xor_sync(0xffffffffu, s4, 1);
         s4 += __shfl_xor_sync(0xffffffffu, s4, 2);
+#endif
         if (in) {
             float4 dd;
             dd.x = fmaf(-pe, prev, x.x);
             dd.y = fmaf(-pe, x.x, x.y);
             dd.z = fmaf(-pe, x.y, x.z);
             dd.w = fmaf(-pe, x.z, x.w);
-            *reinterpret_cast<float4*>(D + u + 16 * ((u >= 320) + (u >= 640))) = dd;
-            if ((lane & 3) == 0) BS[U0 / 16 + (L >> 2)] = s4;
+            // the iteration's first / last float4 decide at compile time which pieces it can touch
+            constexpr int kU0 = U0;
+            const int u_first = kU0 + 128 * it, u_last = u_first + 124;
+            float* dst;
+            if (u_last < kOverlapSamples) dst = p_lo + u;
+            else if (u_first >= kStepSamples) dst = p_hi + u;
+            else if (u_first >= 320 && u_last < kStepSamples) dst = p_mid + 16 + u;
+            else if (u_first >= kOverlapSamples && u_last < 320) dst = p_mid + u;
+            else dst = (u < kOverlapSamples) ? p_lo + u : (u < kStepSamples ? p_mid + u + (u >= 320 ? 16 : 0) : p_hi + u);
+            *reinterpret_cast<float4*>(dst) = dd;
+            if ((lane & 3) == 0) {
+                const int blk = U0 / 16 + (L >> 2);
+                BSp[blk] = s4;
+                if (u_last >= kStepSamples && blk >= kStepSamples / 16) BSo[blk - kStepSamples / 16] = s4;
+            }
             // u % 160 == 0  <=>  (U0/4 + L) % 40 == 0: at most one lane per iteration, known at compile time
             const int q = (U0 / 4 + 32 * it + 39) / 40;  // first multiple of 40 at or after this iteration's first float4
-            if (U0 / 4 + L == 40 * q) XS[q] = c1 * x.x;
+            if (U0 / 4 + L == 40 * q) {
+                if (q < 4) XSp[q] = c1 * x.x;
+                else XSo[q - 4] = c1 * x.x;
+            }
         }
     }
     if (Geo::kLastLane != 31) carry = __shfl_sync(0xffffffffu, last_w, Geo::kLastLane);
-}
-
-// the 240 samples (and their block sums / frame-start values) the next group shares with this one move to the front
-__device__ __forceinline__ void stage_shift(int lane, float* __restrict__ D, float* __restrict__ BS, float* __restrict__ XS) {
-    if (lane < 30) {
-        const float4 v0 = *reinterpret_cast<const float4*>(D + dpad(kStepSamples) + 4 * lane);
-        const float4 v1 = *reinterpret_cast<const float4*>(D + dpad(kStepSamples) + 4 * (lane + 30));
-        *reinterpret_cast<float4*>(D + 4 * lane) = v0;
-        *reinterpret_cast<float4*>(D + 4 * (lane + 30)) = v1;
-    }
-    const float bsv = BS[kStepSamples / 16 + (lane < 15 ? lane : 0)];
-    const float xsv = XS[4 + (lane & 1)];
-    if (lane < 15) BS[lane] = bsv;
-    if (lane < 2) XS[lane] = xsv;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -808,15 +838,14 @@ __device__ __forceinline__ void trace_end(const StreamParams& p, const int* cs, 
 
 constexpr int kStageIters = StageGeom<kOverlapSamples, kGroupSamples>::kIters;  // float4 per lane and waveform of one step
 
-// one live group whose window is staged: frame means, pass 1, (shift), pass 2, power, (prefetch), mel, epilogue.
+// one live group whose window is staged: frame means, pass 1, pass 2, power, (prefetch), mel, epilogue.
 // Everything it needs beyond the kernel parameters comes from the warp's shared-memory state (CS_*).  The prefetch
 // leaves the next group's 640 new samples in ra / rc; the caller commits them at the top of its next step.
 template <bool MELSPEC, class S, bool TRACE, int OUT>
 __device__ __forceinline__ void process_group(const StreamParams& p, const float* TAB, float* WS, int lane, const int b, const int gn,
                                               typename Pcm<S>::reg_t (&ra)[kStageIters], typename Pcm<S>::reg_t (&rc)[kStageIters]) {
-    float* D = WS + kWsD;
-    float* BS = WS + kWsBS;
-    float* XS = WS + kWsXS;
+    const int par = (gn >> 2) & 1;
+    const float* BS = WS + kWsBS + par * kBsFloats;
     int* cs = reinterpret_cast<int*>(WS + kWsCS);
     float* EX = WS + kWsEX;
     const int h = lane >> 4, n2 = lane & 15;
@@ -836,12 +865,8 @@ __device__ __forceinline__ void process_group(const StreamParams& p, const float
     }
     {
         cf z[32];
-        pair_pass1(n2, h, D, XS, TAB + kTabWin, cmu_x, cmu_y, z);
-        __syncwarp();  // EX aliases D: every lane has its samples in registers ...
-        if (gn & kNextLive) {
-            stage_shift(lane, D, BS, XS);  // ... and the part the next group shares has moved below kWsEX
-            __syncwarp();
-        }
+        pair_pass1(n2, h, par, WS, TAB + kTabWin, cmu_x, cmu_y, z);
+        __syncwarp();  // EX aliases the middle piece of the staged samples: every lane has its samples in registers
         pair_pass1_store(n2, TAB + kTabTwz, EX + h * kExSecondPair, z);
     }
     __syncwarp();
@@ -916,7 +941,7 @@ __global__ void __launch_bounds__(kThreads, 4)
     int* cs = reinterpret_cast<int*>(WS + kWsCS);
     // The next launch on the stream may begin as soon as SMs free up (only effective when the host launched it with
     // programmatic stream serialization, which it does only when that launch cannot conflict with this one).
-    asm volatile("griddepcontrol.launch_dependents;");
+    pdl_release();
     // ---- prologue: the table copy and the partition search overlap (both are round trips to L2) ----
     const int n4 = p.tab_floats / 4;
     const float4* tsrc = reinterpret_cast<const float4*>(p.tab);
@@ -962,6 +987,7 @@ __global__ void __launch_bounds__(kThreads, 4)
     __syncthreads();
     if (!has_work) {
         if (TRACE && p.trace) trace_end(p, cs, lane);
+        pdl_join();
         return;
     }
     int loaded_b = -1;
@@ -1014,9 +1040,7 @@ __global__ void __launch_bounds__(kThreads, 4)
             MixState<S> m = load_mix<S>(cs, p.wav);
             const int S0 = g * kStepSamples;
             const bool full = window_full(m, S0);
-            float* D = WS + kWsD;
-            float* BS = WS + kWsBS;
-            float* XS = WS + kWsXS;
+            const int par = g & 1;
             float carry;
             if (!staged) {  // cold start of a run of groups: the whole window is loaded here, nothing was prefetched
                 constexpr int NH = StageGeom<0, kOverlapSamples>::kIters;
@@ -1039,13 +1063,13 @@ __global__ void __launch_bounds__(kThreads, 4)
                     cs_set(cs, CS_SUB1, __float_as_int(m.sub1), lane);
                 }
                 carry = 0.f;
-                if (full) stage_commit<EXACT, 0, kOverlapSamples, true>(m, S0, lane, p.preemph, p.c1, ha, hc, D, BS, XS, carry);
-                else stage_commit<EXACT, 0, kOverlapSamples, false>(m, S0, lane, p.preemph, p.c1, ha, hc, D, BS, XS, carry);
+                if (full) stage_commit<EXACT, 0, kOverlapSamples, true>(m, S0, lane, p.preemph, p.c1, ha, hc, WS, par, carry);
+                else stage_commit<EXACT, 0, kOverlapSamples, false>(m, S0, lane, p.preemph, p.c1, ha, hc, WS, par, carry);
             } else {
                 carry = cs_f(cs, CS_CARRY);
             }
-            if (full) stage_commit<EXACT, kOverlapSamples, kGroupSamples, true>(m, S0, lane, p.preemph, p.c1, ra, rc, D, BS, XS, carry);
-            else stage_commit<EXACT, kOverlapSamples, kGroupSamples, false>(m, S0, lane, p.preemph, p.c1, ra, rc, D, BS, XS, carry);
+            if (full) stage_commit<EXACT, kOverlapSamples, kGroupSamples, true>(m, S0, lane, p.preemph, p.c1, ra, rc, WS, par, carry);
+            else stage_commit<EXACT, kOverlapSamples, kGroupSamples, false>(m, S0, lane, p.preemph, p.c1, ra, rc, WS, par, carry);
             if (TRACE && p.trace) trace_phase(p, cs, lane, 5);
             budget -= p.cm.live + (run_start(dq.y, dq.z, g) ? p.cm.cold : 0);
             next_live = (g + 1 < p.G) && !is_dead(dq.y, dq.z, dq.w, g + 1) && budget > 0;
@@ -1064,6 +1088,7 @@ __global__ void __launch_bounds__(kThreads, 4)
         __syncwarp();
     }
     if (TRACE && p.trace) trace_end(p, cs, lane);
+    pdl_join();
 }
 
 }  // namespace psla

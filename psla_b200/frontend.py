@@ -119,6 +119,7 @@ class GpuFbankFrontend:
         self.set_fast_log(fast_log)
         self.set_exact_clip_mean(exact_clip_mean)
         self.output_layout = "tf"
+        self.launch_overlap = "call"
         self._ws = {}
 
     # ---- lifetime ----
@@ -179,9 +180,17 @@ class GpuFbankFrontend:
         """Descriptor upload on the library's copy stream (default) or on the launch stream (psla_frontend_set_meta_stream)."""
         _lib.check(self.lib.psla_frontend_set_meta_stream(self._h, int(bool(enable))), "set_meta_stream", self._h)
 
-    def set_launch_overlap(self, enable: bool):
-        """Programmatic overlap of consecutive launches (psla_frontend_set_launch_overlap)."""
-        _lib.check(self.lib.psla_frontend_set_launch_overlap(self._h, int(bool(enable))), "set_launch_overlap", self._h)
+    def set_launch_overlap(self, mode="call"):
+        """Programmatic overlap of consecutive launches (psla_frontend_set_launch_overlap):
+          "off" / False   plain launches
+          "call" / True   (default) between the chunks of one forward call (batches above 128 clips)
+          "stream"        also between consecutive forward calls on the same stream -- only if nothing enqueued on that
+                          stream in between releases its own dependents early (see include/psla_frontend.h)."""
+        modes = {"off": 0, False: 0, 0: 0, "call": 1, True: 1, 1: 1, "stream": 2, 2: 2}
+        if mode not in modes:
+            raise ValueError('mode must be "off", "call" or "stream"')
+        self.launch_overlap = ("off", "call", "stream")[modes[mode]]
+        _lib.check(self.lib.psla_frontend_set_launch_overlap(self._h, modes[mode]), "set_launch_overlap", self._h)
 
     def set_param_meta(self, enable: bool):
         """Clip descriptors of small batches as kernel parameters (default) or uploaded (psla_frontend_set_param_meta)."""

@@ -69,7 +69,7 @@ def main():
         fe.set_param_meta(on)
         us = time_steps()
         print(f"descriptors as kernel parameters: {on}: {us:.2f} us/step")
-    for on in (True, False, True):
+    for on in ("stream", "off", "stream"):
         fe.set_launch_overlap(on)
         us = time_steps()
         torch.cuda.synchronize()
@@ -80,13 +80,13 @@ def main():
         torch.cuda.synchronize()
         print(f"launch overlap: {on}: {us:.2f} us/step; host time per call (3 calls, queue empty) {(t1 - t0) / 3 * 1e6:.1f} us")
     # overlapped launches must give the same results as plain ones
-    fe.set_launch_overlap(False)
+    fe.set_launch_overlap("off")
     plain = []
     for k in range(4):
         fe.forward_packed(sets[k], src1, src2, lam, masks, out=outs[k])
     torch.cuda.synchronize()
     plain = [o.clone() for o in outs]
-    fe.set_launch_overlap(True)
+    fe.set_launch_overlap("stream")
     for rep in range(5):
         for k in range(4):
             outs[k].zero_()

@@ -42,20 +42,20 @@ int emu_fbank(const float* x, int n, int num_bins, const float* mel_dense, const
     const float c1 = static_cast<float>(1.0 - static_cast<double>(p));
     const float eps = 1.1920928955078125e-07f;
     std::vector<float> W(kWarpFloats, 0.f);
-    float* D = W.data() + kWsD;
-    float* BS = W.data() + kWsBS;
-    float* XS = W.data() + kWsXS;
     float* EX = W.data() + kWsEX;
 
     for (int f0 = 0; f0 < m; f0 += kGroupFrames) {
         const int S0 = f0 * kFrameShift;
+        const int par = (f0 / kGroupFrames) & 1;  // the kernel alternates its two overlap buffers from group to group
+        float* BS = W.data() + kWsBS + par * kBsFloats;
+        float* XS = W.data() + kWsXS + par * kXsFloats;
         // ---- staging (scalar restatement of the kernel's warp-private staging) ----
         for (int u = 0; u < kGroupSamples; ++u) {
             const int s = S0 + u;
             const float xc = s < n ? x[s] : 0.f;
             const float xp = (u > 0 && s - 1 < n) ? x[s - 1] : 0.f;
-            D[dpad(u)] = fmaf(-p, xp, xc);
-            if (u % kFrameShift == 0) XS[u / kFrameShift] = c1 * xc;
+            W[wpos(u, par)] = fmaf(-p, xp, xc);
+            if (u % kFrameShift == 0 && u < kStepSamples) XS[u / kFrameShift] = c1 * xc;
         }
         for (int q = 0; q < kGroupSamples / 16; ++q) {
             // same association as the kernel: 4 x (sum of 4) combined by two xor-shuffle steps
@@ -86,11 +86,11 @@ int emu_fbank(const float* x, int n, int num_bins, const float* mel_dense, const
         }
         cf regs[32][2][16];
         static cf z1[32][32];
-        for (int lane = 0; lane < 32; ++lane) {  // pass 1 (reads D)
+        for (int lane = 0; lane < 32; ++lane) {  // pass 1 (reads the staged samples)
             const int h = lane >> 4, n2 = lane & 15;
-            pair_pass1(n2, h, D, XS, TAB + kTabWin, cmu[2 * h], cmu[2 * h + 1], z1[lane]);
+            pair_pass1(n2, h, par, W.data(), TAB + kTabWin, cmu[2 * h], cmu[2 * h + 1], z1[lane]);
         }
-        for (int lane = 0; lane < 32; ++lane) {  // pass 1 stores (EX aliases D)   -- __syncwarp --
+        for (int lane = 0; lane < 32; ++lane) {  // pass 1 stores (EX aliases the middle of the window)   -- __syncwarp --
             const int h = lane >> 4, n2 = lane & 15;
             pair_pass1_store(n2, TAB + kTabTwz, EX + h * kExSecondPair, z1[lane]);
         }

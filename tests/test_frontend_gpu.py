@@ -291,14 +291,16 @@ def test_launch_plumbing_does_not_change_results(fe):
     args = (packed, s1, s2, lam[:n], masks[:n])
     ref = fe.forward_packed(*args, target_length=200).cpu()
     try:
-        for setter, val in ((fe.set_param_meta, False), (fe.set_launch_overlap, False), (fe.set_meta_stream, False)):
+        for setter, val, back in ((fe.set_param_meta, False, True), (fe.set_launch_overlap, "off", "stream"),
+                                  (fe.set_launch_overlap, "call", "stream"), (fe.set_meta_stream, False, True)):
             setter(val)
             outs = [torch.empty(n, 200, 128, device=fe.device) for _ in range(3)]
             for o in outs:  # back-to-back launches into different buffers (what the overlap path keys on)
                 fe.forward_packed(*args, out=o, target_length=200)
             torch.cuda.synchronize()
             assert all(torch.equal(o.cpu(), ref) for o in outs)
-            setter(True)
+            setter(back)
+        # from here on consecutive calls may overlap (PSLA_OVERLAP_STREAM: nothing but our own launches on the stream)
         outs = [torch.empty(n, 200, 128, device=fe.device) for _ in range(4)]
         for rep in range(3):
             for o in outs:
@@ -321,9 +323,75 @@ def test_launch_plumbing_does_not_change_results(fe):
         assert torch.equal(fe.forward_packed(*args, target_length=200).cpu(), ref)
     finally:
         fe.set_param_meta(True)
-        fe.set_launch_overlap(True)
+        fe.set_launch_overlap("call")
         fe.set_meta_stream(True)
         fe.set_cost_model(64, 2, 48)
+
+
+def test_overlapping_launches_keep_stream_order(FE):
+    """PSLA_OVERLAP_STREAM (include/psla_frontend.h): a launch may START while its predecessor still runs, but it joins
+    that predecessor before it exits, so (a) whatever is enqueued next sees every earlier launch finished -- checked with
+    one heavy launch followed by tiny ones into rotating and aliasing buffers and an immediate consumer -- and (b) a
+    plain kernel enqueued between two calls (here: torch kernels that REWRITE the waveform buffer) is waited for in full."""
+    fe = FE({"num_mel_bins": 128, "target_length": 400, "mean": MEAN, "std": STD})
+    fe.set_launch_overlap("stream")
+    dev = fe.device
+    from psla_b200.frontend import PackedWaves, pack_waveforms
+    T = 400
+    heavy_waves = [synth_wave(100 + s, 64000, ("gauss", "am")[s % 2]) for s in range(96)]
+    tiny_waves = [synth_wave(300 + s, 8000 + 160 * s) for s in range(6)]
+    heavy, tiny = pack_waveforms(heavy_waves, device=dev), pack_waveforms(tiny_waves, device=dev)
+    s_heavy = np.arange(96, dtype=np.int32)
+    fe.set_launch_overlap("off")
+    ref_heavy = fe.forward_packed(heavy, s_heavy, target_length=T).clone()
+    ref_tiny = [fe.forward_packed(tiny, np.array([i], np.int32), target_length=T).clone() for i in range(6)]
+    torch.cuda.synchronize()
+    fe.set_launch_overlap("stream")
+    # (a) heavy, then 6 tiny launches: rotating over 3 buffers (every buffer written twice), consumer right behind
+    out_heavy = torch.empty(96, T, 128, device=dev)
+    bufs = [torch.empty(1, T, 128, device=dev) for _ in range(3)]
+    for rep in range(40):
+        out_heavy.zero_()
+        for b_ in bufs:
+            b_.zero_()
+        fe.forward_packed(heavy, s_heavy, out=out_heavy, target_length=T)
+        for k in range(6):
+            fe.forward_packed(tiny, np.array([k], np.int32), out=bufs[k % 3], target_length=T)
+        got_heavy = out_heavy.clone()  # a consumer kernel directly behind the tiny launches: the heavy one must be done
+        got = [b_.clone() for b_ in bufs]
+        torch.cuda.synchronize()
+        assert torch.equal(got_heavy, ref_heavy), rep
+        for j in range(3):
+            assert torch.equal(got[j], ref_tiny[3 + j]), (rep, j)  # the LAST writer of each buffer
+    # ... and aliasing: tiny launches writing INTO the heavy launch's output range go out as plain launches
+    for rep in range(10):
+        fe.forward_packed(heavy, s_heavy, out=out_heavy, target_length=T)
+        for k in range(4):
+            fe.forward_packed(tiny, np.array([k], np.int32), out=out_heavy[10 * k:10 * k + 1], target_length=T)
+        torch.cuda.synchronize()
+        expect = ref_heavy.clone()
+        for k in range(4):
+            expect[10 * k] = ref_tiny[k][0]
+        assert torch.equal(out_heavy, expect), rep
+    # (b) a producer kernel between two calls rewrites the waveform buffer the second call reads
+    n = 64000
+    a_src = torch.stack([w.reshape(-1) for w in heavy_waves[:48]]).to(dev)
+    b_src = torch.stack([w.reshape(-1) for w in heavy_waves[48:]]).to(dev)
+    offs, lens = np.arange(48, dtype=np.int64) * n, np.full(48, n, dtype=np.int64)
+    s48 = np.arange(48, dtype=np.int32)
+    buf = torch.empty(48 * n, device=dev)
+    pk = PackedWaves(buf, offs, lens)
+    o1, o2 = torch.empty(48, T, 128, device=dev), torch.empty(48, T, 128, device=dev)
+    for rep in range(40):
+        buf.view(48, n).copy_(b_src if rep % 2 else a_src)
+        torch.cuda.synchronize()
+        first, second = (b_src, a_src) if rep % 2 else (a_src, b_src)
+        fe.forward_packed(pk, s48, out=o1, target_length=T)
+        torch.add(second, 0.0, out=buf.view(48, n))  # an elementwise KERNEL (not a memcpy) overwriting the input
+        fe.forward_packed(pk, s48, out=o2, target_length=T)
+        torch.cuda.synchronize()
+        r1, r2 = (ref_heavy[48:], ref_heavy[:48]) if rep % 2 else (ref_heavy[:48], ref_heavy[48:])
+        assert torch.equal(o1, r1) and torch.equal(o2, r2), rep
 
 
 def test_c2_audioset_train_batch(fe):

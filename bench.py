@@ -53,6 +53,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--repeats", type=int, default=50, help="how many times the --steps timed region is repeated (median reported)")
     ap.add_argument("--sustained-seconds", type=float, default=2.0, help="length of the back-to-back sustained run (0 = skip)")
+    ap.add_argument("--loader-seconds", type=float, default=3.0, help="length of the worker-fed dataloader run (0 = skip)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="bounded CPU-baseline sample (main arm, N=1)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -429,6 +430,27 @@ def run_b200(args):
     h2d = N_WAV * N_SAMPLES * 2
     d2h = B_CLIPS * T_FRAMES * N_MEL * 4
 
+    # ---- e2e through the dataloader: wav files -> worker processes -> pinned shared slots -> side-stream H2D -> kernel ----
+    # (what the reference's training loop does at src/run.py:82-94 / src/traintest.py:81-88; features stay on the GPU)
+    loader_rec = None
+    if args.loader_seconds > 0:
+        sys.path.insert(0, os.path.join(ROOT, "scripts"))
+        import loader_bench
+
+        cores = len(os.sched_getaffinity(0))
+        try:
+            barrier()
+            lr = loader_bench.run(dev, seconds=args.loader_seconds, workers=max(1, cores // world - 1), n_files=200, rank=rank)
+            barrier()
+            total = lr["value"]
+            if world > 1:
+                t = torch.tensor([lr["value"]], dtype=torch.float64, device=dev)
+                dist.all_reduce(t, op=dist.ReduceOp.SUM)
+                total = float(t.item())
+            loader_rec = dict(lr, value=total, per_rank_value=lr["value"], workers_per_rank=lr["workers"])
+        except Exception as exc:  # the sub-record is informative; the contract's keys do not depend on it
+            loader_rec = {"error": f"{type(exc).__name__}: {exc}"}
+
     sampler.stop_flag = True
     sampler.join(timeout=1.0)
     clocks = sampler.summary(t_host0, t_host1)
@@ -453,6 +475,7 @@ def run_b200(args):
                                                  "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                                                  "note": "same call with out_host = NULL: features left on the device for the model, "
                                                          "one fp32 checksum per step read back"},
+                        "dataloader": loader_rec,
                         "numa": numa_note,
                         "note": "pinned host 16-bit PCM -> psla_frontend_forward_host_pcm16 -> pinned host fp32 features; "
                                 "PCIe-bound (descriptors travel as kernel parameters)"},

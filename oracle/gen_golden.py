@@ -10,6 +10,8 @@ What is pinned (the reference has no tests of its own):
   * tables.npz        -- ``kaldi.get_mel_banks`` nnz + ``torch.hann_window`` as used by the call
   * mask_offsets.npz  -- cells masked by the real Frequency/TimeMasking modules for 200 seeds
   * getitem_*.npz     -- full ``AudiosetDataset.__getitem__`` outputs on a tiny in-memory dataset
+  * getitem_files.npz -- the same class reading REAL 16-bit wav files (written by psla_b200.synth.write_tiny_wav_dataset;
+                         ``torchaudio.load`` replaced by a wav reader with its int16 normalisation, value / 32768)
 """
 from __future__ import annotations
 
@@ -139,16 +141,59 @@ def gen_getitem(AudiosetDataset, only=None):
             print("getitem", name, np.stack(feats).shape)
 
 
+def gen_getitem_files(AudiosetDataset):
+    """The unmodified reference class over real wav files: eval conf (deterministic) and train conf (seeded, single process)."""
+    import wave
+
+    from psla_b200.synth import write_tiny_wav_dataset
+
+    def load_wav(path):  # what torchaudio.load(path) returns for a mono 16-bit PCM file (normalize=True)
+        with wave.open(path, "rb") as f:
+            assert f.getsampwidth() == 2 and f.getnchannels() == 1
+            sr = f.getframerate()
+            data = np.frombuffer(f.readframes(f.getnframes()), dtype="<i2")
+        return torch.from_numpy(data.astype(np.float32) / 32768.0).unsqueeze(0), sr
+
+    with tempfile.TemporaryDirectory() as tmp:
+        jpath, cpath = write_tiny_wav_dataset(tmp, copies=2)
+        torchaudio.load = load_wav
+        out = {}
+        confs = {
+            "eval": {"num_mel_bins": 128, "target_length": 256, "freqm": 0, "timem": 0, "mixup": 0,
+                     "dataset": "audioset", "mode": "evaluation", "mean": -4.6476, "std": 4.5699, "noise": False},
+            "train": {"num_mel_bins": 128, "target_length": 256, "freqm": 24, "timem": 40, "mixup": 0.5,
+                      "dataset": "audioset", "mode": "train", "mean": -4.6476, "std": 4.5699, "noise": False},
+        }
+        for name, conf in confs.items():
+            ds = AudiosetDataset(jpath, audio_conf=conf, label_csv=cpath)
+            random.seed(5)
+            np.random.seed(5)
+            torch.manual_seed(5)
+            feats, labels = [], []
+            for i in range(len(ds)):
+                fb, lab = ds[i]
+                feats.append(fb.numpy())
+                labels.append(lab.numpy())
+            out[f"{name}_feats"], out[f"{name}_labels"], out[f"{name}_conf"] = np.stack(feats), np.stack(labels), json.dumps(conf)
+        np.savez_compressed(os.path.join(GOLD, "getitem_files.npz"), seed=np.array(5), copies=np.array(2), **out)
+        print("getitem_files", out["eval_feats"].shape, out["train_feats"].shape)
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     torch.set_num_threads(1)
     if len(sys.argv) > 1:  # e.g. `python oracle/gen_golden.py noise`: (re)generate only the named __getitem__ fixtures
-        gen_getitem(import_reference_dataset(), only=set(sys.argv[1:]))
+        if "files" in sys.argv[1:]:
+            gen_getitem_files(import_reference_dataset())
+        rest = set(sys.argv[1:]) - {"files"}
+        if rest:
+            gen_getitem(import_reference_dataset(), only=rest)
         return
     gen_fbank_c1()
     gen_tables()
     gen_mask_offsets()
     gen_getitem(import_reference_dataset())
+    gen_getitem_files(import_reference_dataset())
     meta = {"torch": torch.__version__, "torchaudio": torchaudio.__version__, "numpy": np.__version__,
             "reference": "/root/reference (haoheliu/psla), src/dataloaders/audioset_dataset.py unmodified",
             "pinned_in_reference_requirements": "torchaudio==0.6.0 torch==1.6.0 (not installable here)"}

@@ -37,10 +37,10 @@ class PackedWaves:
 
 
 def pack_waveforms(waves: Sequence[torch.Tensor], device: Union[str, torch.device, None] = None,
-                   pinned: bool = False) -> PackedWaves:
+                   pinned: bool = False, out: Optional[torch.Tensor] = None) -> PackedWaves:
     """Pack [1, n] / [n] waveforms (channel 0, as kaldi.fbank selects it, kaldi.py:136) with each start rounded up to
     a multiple of 4 samples so the kernels can use vector loads.  All-int16 input is packed as int16 PCM, anything else
-    as fp32."""
+    as fp32.  `out`: pack into this 1-D host tensor (e.g. a slot of page-locked shared memory) instead of a new one."""
     lens = np.array([int(w.shape[-1]) for w in waves], dtype=np.int64)
     starts = np.zeros(len(waves), dtype=np.int64)
     pos = 0
@@ -48,8 +48,20 @@ def pack_waveforms(waves: Sequence[torch.Tensor], device: Union[str, torch.devic
         starts[i] = pos
         pos += (int(n) + 3) // 4 * 4
     dtype = torch.int16 if len(waves) > 0 and all(w.dtype == torch.int16 for w in waves) else torch.float32
-    flat = torch.zeros(max(pos, 8), dtype=dtype, pin_memory=pinned)
+    if out is not None:
+        if out.dtype != dtype or out.dim() != 1 or out.numel() < max(pos, 8):
+            raise ValueError("out must be a 1-D tensor of the packed dtype with room for the batch")
+        flat = out[:max(pos, 8)]
+        for i in range(len(waves)):  # the gaps between waveforms (start alignment) are never read as samples of a clip
+            flat[starts[i] + lens[i]:(starts[i + 1] if i + 1 < len(waves) else max(pos, 8))] = 0
+    else:
+        flat = torch.zeros(max(pos, 8), dtype=dtype, pin_memory=pinned)
     for i, w in enumerate(waves):
+        if hasattr(w, "read_into"):  # samples still in their file (dataloaders.LazyPcm16): read them into place
+            if dtype == torch.int16:
+                w.read_into(flat[starts[i]:starts[i] + lens[i]])
+                continue
+            w = w.materialize()
         w = w.detach()
         w = w[0] if w.dim() == 2 else w
         flat[starts[i]:starts[i] + lens[i]] = w.to(dtype)

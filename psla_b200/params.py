@@ -34,9 +34,13 @@ class ItemParams:
 def axis_mask(mask_param: int, axis_size: int) -> Tuple[int, int]:
     """(start, width) exactly as torchaudio.functional.mask_along_axis computes them in fp32
     (functional.py:939-943): value = rand*P ; min_value = rand*(size - value) ; long() truncation."""
-    value = torch.rand(1) * mask_param
-    min_value = torch.rand(1) * (axis_size - value)
-    return int(min_value.long()), int(value.long())
+    # the same two draws from torch's global generator, then the same IEEE fp32 products on numpy scalars (a dataloader
+    # worker spends more time in five tiny tensor ops than in decoding the file): bit-identical to the tensor expression,
+    # checked against the real FrequencyMasking / TimeMasking modules over 200 seeds (tests/golden/mask_offsets.npz)
+    r1, r2 = np.float32(torch.rand(1).item()), np.float32(torch.rand(1).item())
+    value = r1 * np.float32(mask_param)
+    min_value = r2 * (np.float32(axis_size) - value)
+    return int(min_value), int(value)
 
 
 def draw_masks(freqm: int, timem: int, num_mel_bins: int, target_length: int) -> Tuple[int, int, int, int]:

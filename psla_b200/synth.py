@@ -40,3 +40,39 @@ TINY_LABELS = ("/m/c0", "/m/c1,/m/c2", "/m/c3", "/m/c0,/m/c4", "/m/c5", "/m/c6,/
 
 def tiny_dataset_waves() -> List[torch.Tensor]:
     return [synth_wave(100 + i, n, KINDS[i % 3]) for i, n in enumerate(TINY_LENGTHS)]
+
+
+def write_wav16(path: str, wave: torch.Tensor, sample_rate: int = SAMPLE_RATE) -> None:
+    """[1, n] / [n] float32 in [-1, 1) -> mono 16-bit PCM wav file (round to nearest, saturate): what the recipes'
+    resampled 16 kHz files are (egs/*/prep_*.py)."""
+    import wave as _wave
+
+    pcm = torch.clamp(torch.round(wave.reshape(-1).to(torch.float32) * 32768.0), -32768, 32767).to(torch.int16)
+    with _wave.open(path, "wb") as f:
+        f.setnchannels(1)
+        f.setsampwidth(2)
+        f.setframerate(sample_rate)
+        f.writeframes(pcm.numpy().astype("<i2").tobytes())
+
+
+def write_tiny_wav_dataset(directory: str, copies: int = 1):
+    """The tiny dataset as real files: 8 * copies 16-bit wav files + manifest json + label csv in `directory`.
+    Returns (json_path, csv_path).  Shared by oracle/gen_golden.py (reference side) and the dataloader tests."""
+    import json
+    import os
+
+    waves = tiny_dataset_waves()
+    data = []
+    for c in range(copies):
+        for i, w in enumerate(waves):
+            path = os.path.join(directory, f"clip_{c}_{i}.wav")
+            write_wav16(path, w)
+            data.append({"wav": path, "labels": TINY_LABELS[i]})
+    jpath, cpath = os.path.join(directory, "tiny_files.json"), os.path.join(directory, "labels.csv")
+    with open(jpath, "w") as f:
+        json.dump({"data": data}, f)
+    with open(cpath, "w") as f:
+        f.write("index,mid,display_name\n")
+        for i, mid in enumerate(TINY_CLASSES):
+            f.write(f"{i},{mid},class{i}\n")
+    return jpath, cpath

@@ -61,6 +61,8 @@ size_t psla_frontend_workspace_bytes(const psla_frontend_t* handle, int n_clips)
  * (audioset_dataset.py:88-137, :177-192) for B clips.
  *
  *   wav         DEVICE  packed fp32 waveforms in [-1, 1] (what torchaudio.load returns, channel 0), 16-byte aligned
+ *   wav_samples         number of samples `wav` holds: every (offset, length) pair is checked against it, a descriptor that
+ *                       reaches past the buffer is PSLA_E_INVALID (never an out-of-bounds device read)
  *   wav_offset  HOST    [n_wav] start sample of every waveform inside `wav` (a multiple of 4 enables 128-bit loads)
  *   wav_length  HOST    [n_wav] number of samples of every waveform
  *   src1        HOST    [B] primary waveform index of each output clip
@@ -71,7 +73,7 @@ size_t psla_frontend_workspace_bytes(const psla_frontend_t* handle, int n_clips)
  *   norm_mean, norm_div  fbank = (fbank - norm_mean) / norm_div unless skip_norm                 (:191-192)
  *   out         DEVICE  [B][target_length][num_mel_bins] fp32, 16-byte aligned
  */
-int psla_frontend_forward(psla_frontend_t* handle, const float* wav, const int64_t* wav_offset, const int64_t* wav_length, int n_wav,
+int psla_frontend_forward(psla_frontend_t* handle, const float* wav, int64_t wav_samples, const int64_t* wav_offset, const int64_t* wav_length, int n_wav,
                           const int32_t* src1, const int32_t* src2, const double* lambda, const int32_t* mask,
                           int n_clips, int target_length, float norm_mean, float norm_div, int skip_norm,
                           float* out, void* workspace, size_t workspace_bytes, void* stream);
@@ -80,7 +82,7 @@ int psla_frontend_forward(psla_frontend_t* handle, const float* wav, const int64
  * owns the device staging buffers (grown on demand, kept in the handle).  `out_host` may be NULL to leave the
  * features on the device; psla_frontend_device_out() then returns the device pointer (valid until the next
  * forward_host call on the same handle).  Asynchronous on `stream`. */
-int psla_frontend_forward_host(psla_frontend_t* handle, const float* wav_host, const int64_t* wav_offset, const int64_t* wav_length,
+int psla_frontend_forward_host(psla_frontend_t* handle, const float* wav_host, int64_t wav_samples, const int64_t* wav_offset, const int64_t* wav_length,
                                int n_wav,
                                const int32_t* src1, const int32_t* src2, const double* lambda, const int32_t* mask,
                                int n_clips, int target_length, float norm_mean, float norm_div, int skip_norm,
@@ -91,11 +93,11 @@ float* psla_frontend_device_out(const psla_frontend_t* handle);
  * torchaudio.load, audioset_dataset.py:91,95-96, whose normalisation is value / 32768; the kernel applies exactly that
  * scale, so the features equal those of the fp32 entry points fed with the decoded floats bit for bit).  Half the input
  * bytes over PCIe and HBM.  Offsets and lengths are in samples; `wav` 16-byte aligned. */
-int psla_frontend_forward_pcm16(psla_frontend_t* handle, const int16_t* wav, const int64_t* wav_offset, const int64_t* wav_length,
+int psla_frontend_forward_pcm16(psla_frontend_t* handle, const int16_t* wav, int64_t wav_samples, const int64_t* wav_offset, const int64_t* wav_length,
                                 int n_wav, const int32_t* src1, const int32_t* src2, const double* lambda, const int32_t* mask,
                                 int n_clips, int target_length, float norm_mean, float norm_div, int skip_norm,
                                 float* out, void* workspace, size_t workspace_bytes, void* stream);
-int psla_frontend_forward_host_pcm16(psla_frontend_t* handle, const int16_t* wav_host, const int64_t* wav_offset,
+int psla_frontend_forward_host_pcm16(psla_frontend_t* handle, const int16_t* wav_host, int64_t wav_samples, const int64_t* wav_offset,
                                      const int64_t* wav_length, int n_wav, const int32_t* src1, const int32_t* src2,
                                      const double* lambda, const int32_t* mask, int n_clips, int target_length, float norm_mean,
                                      float norm_div, int skip_norm, float* out_host, void* stream);
@@ -134,9 +136,10 @@ int psla_frontend_set_fast_log(psla_frontend_t* handle, int enable);
 int psla_frontend_set_output_layout(psla_frontend_t* handle, int layout);
 
 /* Whole-clip DC removal (audioset_dataset.py:92 / :98-99 / :117).  Every constant the reference subtracts from a whole
- * clip is removed again by kaldi.fbank's per-frame DC removal (kaldi.py:183-186), so the default (0) subtracts the
- * clip's first sample instead of its mean -- same features up to fp32 rounding, no extra pass over the waveform; clip
- * statistics are then computed only for mixup clips whose partner is shorter (its mean fills the zero-padded tail).
+ * clip is removed again by kaldi.fbank's per-frame DC removal (kaldi.py:183-186), so the default (0) subtracts a
+ * five-sample median of the clip (first, quartile and last samples: robust against a click or a loud onset) instead of
+ * its mean -- same features up to fp32 rounding, no extra pass over the waveform; clip statistics are then computed
+ * only for mixup clips whose partner is shorter (its mean fills the zero-padded tail).
  * 1 = compute the three means with a statistics kernel and evaluate the reference's fp32 expression verbatim. */
 int psla_frontend_set_exact_clip_mean(psla_frontend_t* handle, int enable);
 

@@ -22,17 +22,17 @@ SYMBOLS = {
     "psla_frontend_set_tables": (c_int, [c_void_p, c_void_p, c_void_p]),
     "psla_frontend_get_tables": (c_int, [c_void_p, c_void_p, c_void_p]),
     "psla_frontend_workspace_bytes": (c_size_t, [c_void_p, c_int]),
-    "psla_frontend_forward": (c_int, [c_void_p, c_void_p, POINTER(c_int64), POINTER(c_int64), c_int, POINTER(c_int32), POINTER(c_int32),
+    "psla_frontend_forward": (c_int, [c_void_p, c_void_p, c_int64, POINTER(c_int64), POINTER(c_int64), c_int, POINTER(c_int32), POINTER(c_int32),
                                       POINTER(c_double), POINTER(c_int32), c_int, c_int, c_float, c_float, c_int,
                                       c_void_p, c_void_p, c_size_t, c_void_p]),
-    "psla_frontend_forward_host": (c_int, [c_void_p, c_void_p, POINTER(c_int64), POINTER(c_int64), c_int, POINTER(c_int32), POINTER(c_int32),
+    "psla_frontend_forward_host": (c_int, [c_void_p, c_void_p, c_int64, POINTER(c_int64), POINTER(c_int64), c_int, POINTER(c_int32), POINTER(c_int32),
                                            POINTER(c_double), POINTER(c_int32), c_int, c_int, c_float, c_float, c_int,
                                            c_void_p, c_void_p]),
     "psla_frontend_device_out": (c_void_p, [c_void_p]),
-    "psla_frontend_forward_pcm16": (c_int, [c_void_p, c_void_p, POINTER(c_int64), POINTER(c_int64), c_int, POINTER(c_int32), POINTER(c_int32),
+    "psla_frontend_forward_pcm16": (c_int, [c_void_p, c_void_p, c_int64, POINTER(c_int64), POINTER(c_int64), c_int, POINTER(c_int32), POINTER(c_int32),
                                             POINTER(c_double), POINTER(c_int32), c_int, c_int, c_float, c_float, c_int,
                                             c_void_p, c_void_p, c_size_t, c_void_p]),
-    "psla_frontend_forward_host_pcm16": (c_int, [c_void_p, c_void_p, POINTER(c_int64), POINTER(c_int64), c_int, POINTER(c_int32),
+    "psla_frontend_forward_host_pcm16": (c_int, [c_void_p, c_void_p, c_int64, POINTER(c_int64), POINTER(c_int64), c_int, POINTER(c_int32),
                                                  POINTER(c_int32), POINTER(c_double), POINTER(c_int32), c_int, c_int, c_float, c_float,
                                                  c_int, c_void_p, c_void_p]),
     "psla_frontend_noise_roll": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, POINTER(c_float), POINTER(c_int32), c_int, c_int,

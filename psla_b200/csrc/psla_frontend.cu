@@ -697,7 +697,7 @@ int enqueue_batch(psla_frontend_t* h, const void* wav, bool pcm16, ClipDesc* des
     return PSLA_OK;
 }
 
-int forward_any(psla_frontend_t* h, const void* wav, bool pcm16, const int64_t* wav_offset, const int64_t* wav_length, int n_wav,
+int forward_any(psla_frontend_t* h, const void* wav, int64_t wav_samples, bool pcm16, const int64_t* wav_offset, const int64_t* wav_length, int n_wav,
                 const int32_t* src1, const int32_t* src2, const double* lambda, const int32_t* mask, int n_clips, int target_length,
                 float norm_mean, float norm_div, int skip_norm, float* out, void* workspace, size_t workspace_bytes, void* stream_) {
     if (!h || !wav_offset || !wav_length || !src1 || n_wav < 0 || n_clips < 0 || target_length < 1) return PSLA_E_INVALID;
@@ -728,8 +728,9 @@ int forward_any(psla_frontend_t* h, const void* wav, bool pcm16, const int64_t* 
     bool any_stats = false;
 
     // ---- validate + build descriptors (errors surface synchronously, like the reference's exceptions) ----
+    // every waveform must lie inside the caller's buffer: a bad descriptor is an error here, not an out-of-bounds device read
     for (int i = 0; i < n_wav; ++i)
-        if (wav_offset[i] < 0 || wav_length[i] < 0) return PSLA_E_INVALID;
+        if (wav_offset[i] < 0 || wav_length[i] < 0 || wav_length[i] > wav_samples || wav_offset[i] > wav_samples - wav_length[i]) return PSLA_E_INVALID;
     for (int b = 0; b < n_clips; ++b) {
         ClipDesc& d = descs[b];
         const int a = src1[b];
@@ -837,7 +838,7 @@ int forward_any(psla_frontend_t* h, const void* wav, bool pcm16, const int64_t* 
                          workspace, stream_, false);
 }
 
-int forward_host_any(psla_frontend_t* h, const void* wav_host, bool pcm16, const int64_t* wav_offset, const int64_t* wav_length, int n_wav,
+int forward_host_any(psla_frontend_t* h, const void* wav_host, int64_t wav_samples, bool pcm16, const int64_t* wav_offset, const int64_t* wav_length, int n_wav,
                      const int32_t* src1, const int32_t* src2, const double* lambda, const int32_t* mask, int n_clips, int target_length,
                      float norm_mean, float norm_div, int skip_norm, float* out_host, void* stream_) {
     if (!h || !wav_host || !wav_offset || !wav_length || n_wav < 1 || n_clips < 0 || target_length < 1) return PSLA_E_INVALID;
@@ -847,7 +848,7 @@ int forward_host_any(psla_frontend_t* h, const void* wav_host, bool pcm16, const
     if (!guard.ok) return PSLA_E_CUDA;
     int64_t total = 0;
     for (int i = 0; i < n_wav; ++i) {
-        if (wav_offset[i] < 0 || wav_length[i] < 0) return PSLA_E_INVALID;
+        if (wav_offset[i] < 0 || wav_length[i] < 0 || wav_length[i] > wav_samples || wav_offset[i] > wav_samples - wav_length[i]) return PSLA_E_INVALID;
         if (wav_offset[i] + wav_length[i] > total) total = wav_offset[i] + wav_length[i];
     }
     if (total < 1) return PSLA_E_INVALID;
@@ -873,7 +874,7 @@ int forward_host_any(psla_frontend_t* h, const void* wav_host, bool pcm16, const
     if ((st = grow(reinterpret_cast<void**>(&h->d_out), &h->d_out_cap, out_bytes)) != PSLA_OK) return st;
     if ((st = grow(&h->d_ws, &h->d_ws_cap, ws_bytes)) != PSLA_OK) return st;
     PSLA_CUDA(h, cudaMemcpyAsync(h->d_wav, wav_host, wav_bytes, cudaMemcpyHostToDevice, stream));
-    st = forward_any(h, h->d_wav, pcm16, wav_offset, wav_length, n_wav, src1, src2, lambda, mask, n_clips, target_length, norm_mean, norm_div,
+    st = forward_any(h, h->d_wav, total, pcm16, wav_offset, wav_length, n_wav, src1, src2, lambda, mask, n_clips, target_length, norm_mean, norm_div,
                      skip_norm, h->d_out, h->d_ws, h->d_ws_cap, stream_);
     if (st != PSLA_OK) return st;
     if (out_host) PSLA_CUDA(h, cudaMemcpyAsync(out_host, h->d_out, out_bytes, cudaMemcpyDeviceToHost, stream));
@@ -883,36 +884,36 @@ int forward_host_any(psla_frontend_t* h, const void* wav_host, bool pcm16, const
 
 extern "C" {
 
-int psla_frontend_forward(psla_frontend_t* h, const float* wav, const int64_t* wav_offset, const int64_t* wav_length, int n_wav,
+int psla_frontend_forward(psla_frontend_t* h, const float* wav, int64_t wav_samples, const int64_t* wav_offset, const int64_t* wav_length, int n_wav,
                           const int32_t* src1, const int32_t* src2, const double* lambda, const int32_t* mask, int n_clips,
                           int target_length, float norm_mean, float norm_div, int skip_norm, float* out, void* workspace,
                           size_t workspace_bytes, void* stream) {
-    return forward_any(h, wav, false, wav_offset, wav_length, n_wav, src1, src2, lambda, mask, n_clips, target_length, norm_mean, norm_div,
+    return forward_any(h, wav, wav_samples, false, wav_offset, wav_length, n_wav, src1, src2, lambda, mask, n_clips, target_length, norm_mean, norm_div,
                        skip_norm, out, workspace, workspace_bytes, stream);
 }
 
-int psla_frontend_forward_pcm16(psla_frontend_t* h, const int16_t* wav, const int64_t* wav_offset, const int64_t* wav_length, int n_wav,
+int psla_frontend_forward_pcm16(psla_frontend_t* h, const int16_t* wav, int64_t wav_samples, const int64_t* wav_offset, const int64_t* wav_length, int n_wav,
                                 const int32_t* src1, const int32_t* src2, const double* lambda, const int32_t* mask, int n_clips,
                                 int target_length, float norm_mean, float norm_div, int skip_norm, float* out, void* workspace,
                                 size_t workspace_bytes, void* stream) {
-    return forward_any(h, wav, true, wav_offset, wav_length, n_wav, src1, src2, lambda, mask, n_clips, target_length, norm_mean, norm_div,
+    return forward_any(h, wav, wav_samples, true, wav_offset, wav_length, n_wav, src1, src2, lambda, mask, n_clips, target_length, norm_mean, norm_div,
                        skip_norm, out, workspace, workspace_bytes, stream);
 }
 
 float* psla_frontend_device_out(const psla_frontend_t* h) { return h ? h->d_out : nullptr; }
 
-int psla_frontend_forward_host(psla_frontend_t* h, const float* wav_host, const int64_t* wav_offset, const int64_t* wav_length, int n_wav,
+int psla_frontend_forward_host(psla_frontend_t* h, const float* wav_host, int64_t wav_samples, const int64_t* wav_offset, const int64_t* wav_length, int n_wav,
                                const int32_t* src1, const int32_t* src2, const double* lambda, const int32_t* mask, int n_clips,
                                int target_length, float norm_mean, float norm_div, int skip_norm, float* out_host, void* stream) {
-    return forward_host_any(h, wav_host, false, wav_offset, wav_length, n_wav, src1, src2, lambda, mask, n_clips, target_length, norm_mean,
+    return forward_host_any(h, wav_host, wav_samples, false, wav_offset, wav_length, n_wav, src1, src2, lambda, mask, n_clips, target_length, norm_mean,
                             norm_div, skip_norm, out_host, stream);
 }
 
-int psla_frontend_forward_host_pcm16(psla_frontend_t* h, const int16_t* wav_host, const int64_t* wav_offset, const int64_t* wav_length,
+int psla_frontend_forward_host_pcm16(psla_frontend_t* h, const int16_t* wav_host, int64_t wav_samples, const int64_t* wav_offset, const int64_t* wav_length,
                                      int n_wav, const int32_t* src1, const int32_t* src2, const double* lambda, const int32_t* mask,
                                      int n_clips, int target_length, float norm_mean, float norm_div, int skip_norm, float* out_host,
                                      void* stream) {
-    return forward_host_any(h, wav_host, true, wav_offset, wav_length, n_wav, src1, src2, lambda, mask, n_clips, target_length, norm_mean,
+    return forward_host_any(h, wav_host, wav_samples, true, wav_offset, wav_length, n_wav, src1, src2, lambda, mask, n_clips, target_length, norm_mean,
                             norm_div, skip_norm, out_host, stream);
 }
 

@@ -504,8 +504,17 @@ class FrontendLoader:
         j = self._k % self.n_buffers
         self._k += 1
         nbytes = wav.numel() * wav.element_size()
+        cs = self._copy_stream
+        main = torch.cuda.current_stream(dev)
         if self._dev[j] is None or self._dev[j].numel() < nbytes:
-            self._dev[j] = torch.empty(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=dev)
+            # Allocated ON THE COPY STREAM: the caching allocator hands a block that a main-stream tensor has just freed
+            # straight back to main-stream allocations, because same-stream reuse is ordered -- but the copy below runs
+            # on another stream and would overwrite memory that queued main-stream kernels (the consumer's training
+            # step) still use.  (Seen: NaN weights after the third batch of scripts/c5_train.py.)
+            if self._dev[j] is not None:
+                self._dev[j].record_stream(main)  # its last reader was a kernel on the main stream
+            with torch.cuda.stream(cs):
+                self._dev[j] = torch.empty(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=dev)
             self._dev_free[j] = None
         dst = self._dev[j][:nbytes].view(wav.dtype)
         labels_dev = None
@@ -520,7 +529,6 @@ class FrontendLoader:
             # wake-up costs milliseconds while the dataloader workers keep every core busy -- measured 6 ms vs 0.02 ms)
             ring.numpy()[:lab.numel()] = lab.numpy().reshape(-1)
             lab = ring[:lab.numel()].view(lab.shape)
-        cs = self._copy_stream
         if self._dev_free[j] is not None:
             cs.wait_event(self._dev_free[j])
         with torch.cuda.stream(cs):
@@ -530,9 +538,9 @@ class FrontendLoader:
             ev = torch.cuda.Event()
             ev.record(cs)
         self._pending.append((ev, batch.slot))
-        torch.cuda.current_stream(dev).wait_event(ev)
+        main.wait_event(ev)
         if labels_dev is not None:
-            labels_dev.record_stream(torch.cuda.current_stream(dev))
+            labels_dev.record_stream(main)
         return PackedWaves(dst, batch.waves.offsets, batch.waves.lengths), labels_dev, j
 
     def features(self, batch: RawBatch, with_labels: bool = False):

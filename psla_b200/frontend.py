@@ -269,7 +269,7 @@ class GpuFbankFrontend:
             raise ValueError("waveforms must be float32 or int16 PCM")
         fwd = self.lib.psla_frontend_forward_pcm16 if wav.dtype == torch.int16 else self.lib.psla_frontend_forward
         st = fwd(
-            self._h, wav.data_ptr(), p_off, p_len, packed.n_wav, p1, p2, pl, pm, B, T,
+            self._h, wav.data_ptr(), wav.numel(), p_off, p_len, packed.n_wav, p1, p2, pl, pm, B, T,
             self.norm_mean, self.norm_div, int(self.skip_norm), out.data_ptr(), ws.data_ptr(), ws.numel(), stream)
         _lib.check(st, "psla_frontend_forward", self._h)
         return out
@@ -328,7 +328,7 @@ class GpuFbankFrontend:
             raise ValueError("waveforms must be float32 or int16 PCM")
         fwd = self.lib.psla_frontend_forward_host_pcm16 if wav.dtype == torch.int16 else self.lib.psla_frontend_forward_host
         st = fwd(
-            self._h, wav.data_ptr(), p_off, p_len, packed.n_wav, p1, p2, pl, pm, B, T,
+            self._h, wav.data_ptr(), wav.numel(), p_off, p_len, packed.n_wav, p1, p2, pl, pm, B, T,
             self.norm_mean, self.norm_div, int(self.skip_norm), out_ptr, s)
         _lib.check(st, "psla_frontend_forward_host", self._h)
         if out_host is not None:

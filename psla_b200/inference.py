@@ -10,7 +10,8 @@ copies, overlapping hops allowed), processed `batch` windows per kernel launch. 
 """
 from __future__ import annotations
 
-from typing import Callable, Iterator, List, Optional, Tuple
+from dataclasses import dataclass
+from typing import Callable, Iterator, List, Optional, Sequence, Tuple
 
 import numpy as np
 import torch
@@ -40,6 +41,34 @@ def chunk_offsets(n_samples: int, window: int, hop: Optional[int] = None, keep_t
         i = int(np.argmax(~full))
         keep[i] = lengths[i] >= MIN_SAMPLES
     return starts[keep], lengths[keep]
+
+
+@dataclass
+class RecordingPrediction:
+    """Result of `LongRecordingFrontend.predict`."""
+    starts: np.ndarray        # [W] start sample of every window
+    per_window: torch.Tensor  # [W, C] model output per window (device tensor)
+    clip: Optional[torch.Tensor]  # [C] the recording-level prediction (None when aggregate=None)
+    aggregate: Optional[str]
+
+    def top(self, k: int = 5, names: Optional[Sequence[str]] = None) -> List[Tuple[object, float]]:
+        """The k strongest classes of the recording: (class index or display name, score)."""
+        if self.clip is None:
+            raise ValueError("no recording-level prediction (aggregate=None)")
+        v, i = torch.topk(self.clip.float().cpu(), min(k, self.clip.numel()))
+        return [((names[j] if names is not None else j), float(s)) for s, j in zip(v.tolist(), i.tolist())]
+
+    def timeline(self, class_index: int, sample_rate: int = SAMPLE_RATE) -> List[Tuple[float, float]]:
+        """(window start in seconds, score) of one class over the recording."""
+        col = self.per_window[:, class_index].float().cpu().tolist()
+        return [(float(s) / sample_rate, float(v)) for s, v in zip(self.starts.tolist(), col)]
+
+
+AGGREGATES = {
+    # the reference's models end in a sigmoid per class (Models.py:143-146): per-window outputs are probabilities.
+    "mean": lambda y, w: (y * w.unsqueeze(1)).sum(0) / w.sum(),  # frame-weighted average (a short last window counts less)
+    "max": lambda y, w: y.max(0).values,                         # "does it occur anywhere in the recording"
+}
 
 
 class LongRecordingFrontend:
@@ -83,12 +112,45 @@ class LongRecordingFrontend:
             yield self.starts[lo:hi], self.features(lo, hi)
 
     @torch.no_grad()
-    def predict(self, model: Callable[[torch.Tensor], torch.Tensor], batch: int = 256) -> Tuple[np.ndarray, torch.Tensor]:
-        """Window start samples and per-window model outputs (the model takes [b, target_length, 128] like
-        EffNetAttention.forward, src/models/Models.py:104-107); aggregation over the recording is the caller's choice."""
+    def predict(self, model: Callable[[torch.Tensor], torch.Tensor], batch: int = 256, aggregate: Optional[str] = "mean",
+                overlap_launches: bool = True) -> RecordingPrediction:
+        """One-click inference over the recording: features of `batch` windows per launch -> `model` -> per-window outputs
+        -> one recording-level prediction.  The model takes [b, target_length, 128] like EffNetAttention.forward
+        (src/models/Models.py:104-107) and returns [b, C] (or a tuple whose first element is that, :146).
+        aggregate: "mean" (average over windows, weighted by the number of real frames of each window), "max", or None.
+        The frontend works one batch AHEAD of the model on a second stream, so the kernel of batch k + 1 runs while the
+        model consumes batch k."""
+        if aggregate is not None and aggregate not in AGGREGATES:
+            raise ValueError(f"aggregate must be one of {sorted(AGGREGATES)} or None")
+        dev = self.frontend.device
         outs: List[torch.Tensor] = []
-        for _, feats in self.batches(batch):
+        main = torch.cuda.current_stream(dev)
+        side = torch.cuda.Stream(device=dev) if overlap_launches and len(self) > batch else None
+        ranges = [(lo, min(lo + batch, len(self))) for lo in range(0, len(self), batch)]
+
+        def produce(lo, hi):
+            if side is None:
+                return self.features(lo, hi), None
+            side.wait_stream(main)  # (first call: the recording's upload)
+            with torch.cuda.stream(side):
+                f = self.features(lo, hi)
+                ev = torch.cuda.Event()
+                ev.record(side)
+            return f, ev
+
+        nxt = produce(*ranges[0]) if ranges else None
+        for i in range(len(ranges)):
+            feats, ev = nxt
+            nxt = produce(*ranges[i + 1]) if i + 1 < len(ranges) else None
+            if ev is not None:
+                main.wait_event(ev)
+                feats.record_stream(main)
             y = model(feats)
             outs.append(y[0] if isinstance(y, (tuple, list)) else y)
-        per_window = torch.cat(outs, dim=0) if outs else torch.zeros(0)
-        return self.starts.copy(), per_window
+        per_window = torch.cat(outs, dim=0) if outs else torch.zeros(0, device=dev)
+        clip = None
+        if aggregate is not None and len(outs):
+            frames = np.minimum(np.maximum(1 + (self.lengths - 400) // 160, 0), self.frontend.target_length)
+            w = torch.as_tensor(frames, dtype=per_window.dtype, device=per_window.device)
+            clip = AGGREGATES[aggregate](per_window, w)
+        return RecordingPrediction(self.starts.copy(), per_window, clip, aggregate)

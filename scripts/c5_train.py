@@ -7,11 +7,16 @@ torchvision EfficientNet-B2 trunk with a 1-channel stem plus 4-head attention po
 BCE loss, Adam, bf16 autocast, batch 100 per GPU, input `[B, 1056, 128]` -> `unsqueeze(1).transpose(2, 3)` (:106-107).
 
 Arms (samples/s, 1 process per GPU; under torchrun every rank runs its own slice, gradients all-reduced by DDP):
-  gpu_frontend   pinned host 16-bit PCM batch -> psla_frontend_forward_host_pcm16 (features stay on the GPU) -> train step
-  model_only     features already resident (the ceiling set by the model)
-  cpu_loader     the reference path: oracle port of AudiosetDataset.__getitem__ in a DataLoader with one worker per
-                 host core -> .to(device) (src/traintest.py:81-85) -> train step           (rank 0 / N = 1 only)
-Writes gpurun_out/c5.json.
+  model_only       features already resident (the ceiling set by the model)
+  gpu_frontend     pinned host 16-bit PCM batch -> psla_frontend_forward_host_pcm16 (features stay on the GPU) -> train step
+  loader_frontend  16-bit wav files on tmpfs -> DataLoader workers (cores / ranks - 1 each) -> pinned shared slots ->
+                   side-stream H2D -> fused kernel -> train step with the loader's own soft labels: the reference's loop
+                   (src/traintest.py:81-110) with the dataloaders package swapped
+  cpu_loader       the reference path: oracle port of AudiosetDataset.__getitem__ in ONE DataLoader with one worker per host
+                   core -> .to(device) (src/traintest.py:81-85) -> train step.  At N > 1 the reference scales with
+                   nn.DataParallel in a single process (src/traintest.py:44-45, egs/audioset/run.sh:6,68): rank 0 runs exactly
+                   that over all N GPUs with a global batch of N x 100 while the other ranks wait.
+Writes gpurun_out/c5.json (c5_n<N>.json under torchrun).
 """
 from __future__ import annotations
 
@@ -78,20 +83,30 @@ def main():
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    torch.manual_seed(1 + rank)
-    model = EffNetB2Attention().to(dev).to(memory_format=torch.channels_last)
-    if world > 1:
-        model = nn.parallel.DistributedDataParallel(model, device_ids=[local])
-    opt = torch.optim.Adam(model.parameters(), lr=1e-4, weight_decay=5e-7, betas=(0.95, 0.999))
+    st = {}
+
+    def fresh_model():
+        """Every arm trains its own freshly initialised model (same seed): the arms are independent short runs, and a
+        randomly initialised network fed noise does not stay finite for hundreds of Adam steps."""
+        torch.manual_seed(1)
+        m = EffNetB2Attention().to(dev).to(memory_format=torch.channels_last)
+        st["core"] = m
+        st["model"] = nn.parallel.DistributedDataParallel(m, device_ids=[local]) if world > 1 else m
+        # the reference warms the learning rate up from 0 over its first 1000 steps (traintest.py:90-95): these first few
+        # dozen steps run at ~1e-6 (at 1e-4 from step 0 the randomly initialised stand-in goes non-finite within ten steps
+        # once the labels change from step to step)
+        st["opt"] = torch.optim.Adam(st["model"].parameters(), lr=1e-6, weight_decay=5e-7, betas=(0.95, 0.999))
+
+    fresh_model()
     labels = (torch.rand(B, NCLS, device=dev) < 0.01).float()
 
-    def train_step(feats):
+    def train_step(feats, lab=None):
         with torch.autocast("cuda", dtype=torch.bfloat16):
-            out = model(feats)
-        loss = F.binary_cross_entropy(out.float().clamp(1e-7, 1 - 1e-7), labels)
-        opt.zero_grad(set_to_none=True)
+            out = st["model"](feats)
+        loss = F.binary_cross_entropy(out.float().clamp(1e-7, 1 - 1e-7), labels if lab is None else lab)
+        st["opt"].zero_grad(set_to_none=True)
         loss.backward()
-        opt.step()
+        st["opt"].step()
         return loss
 
     def barrier():
@@ -142,26 +157,103 @@ def main():
         state["k"] += 1
         return train_step(f)
 
+    fresh_model()
     res["gpu_frontend"], res["gpu_frontend_loss"] = timed(gpu_step, steps)
+
+    # ---- wav files -> DataLoader workers -> GPU frontend (the drop-in dataloaders package) ----
+    import tempfile
+    sys.path.insert(0, os.path.join(ROOT, "scripts"))
+    import loader_bench as LB
+    from psla_b200.dataloaders import AudiosetDataset, FrontendLoader, pcm16_lazy_loader
+    cores = len(os.sched_getaffinity(0))
+    workers = max(1, cores // world - 1)
+    conf = {"num_mel_bins": NMEL, "target_length": T, "freqm": 48, "timem": 192, "mixup": 0.5, "dataset": "audioset",
+            "mode": "train", "mean": MEAN, "std": STD, "noise": False}
+    base = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else None
+    with tempfile.TemporaryDirectory(dir=base, prefix=f"psla_c5_{rank}_") as d:
+        jpath, cpath = LB.make_files(d, 200, seed=rank)
+        ds = AudiosetDataset(jpath, conf, label_csv=cpath, loader=pcm16_lazy_loader, verbose=False)
+        sampler = torch.utils.data.WeightedRandomSampler(np.ones(len(ds)), 10 ** 7, replacement=True)  # run.py:84-85 (--bal)
+        fl = FrontendLoader.create(ds, fe, batch_size=B, num_workers=workers, sampler=sampler, prefetch_factor=2)
+        it = iter(fl)
+
+        def loader_step():
+            fb, lab = next(it)
+            if os.environ.get("C5_DEBUG"):
+                torch.cuda.synchronize()
+                print("loader batch: features finite", bool(torch.isfinite(fb).all()), "range", float(fb.min()), float(fb.max()),
+                      "labels range", float(lab.min()), float(lab.max()), "shape", tuple(lab.shape), flush=True)
+                with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+                    o = st["model"](fb)
+                print("  model output finite", bool(torch.isfinite(o).all()), float(o.float().min()), float(o.float().max()), flush=True)
+            mode = os.environ.get("C5_LOADER_MODE", "")
+            if mode == "ignore":
+                return train_step(feats)
+            if mode == "fixed_labels":
+                return train_step(fb)
+            if mode == "fixed_feats":
+                return train_step(feats, lab)
+            if mode == "clone_labels":
+                return train_step(fb, lab.clone())
+            return train_step(fb, lab)
+
+        fresh_model()
+        res["loader_frontend"], res["loader_frontend_loss"] = timed(loader_step, steps, warm=max(3, workers // 2))
+        res["loader_workers_per_rank"] = workers
+        res["loader_data_time_per_sample_us"] = fl.per_sample_data_time.avg * 1e6
+        it.close()
+        fl.close()
+        del it, fl
     fe.close()
 
-    # ---- the reference's CPU dataloader path (rank 0, N = 1) ----
-    if world == 1 and not os.environ.get("C5_NO_CPU"):
-        from oracle import cpu_baseline as CB
-        workers = CB.host_cores()
-        it, sub = CB._loader(dict(CB.TRAIN_CONF), B, workers, 40 * (B + sub_pad(B, workers)))
+    # ---- the reference's CPU dataloader path: one process, one DataLoader over all host cores; nn.DataParallel at N > 1 ----
+    if not os.environ.get("C5_NO_CPU"):
+        barrier()
+        if rank == 0:
+            from oracle import cpu_baseline as CB
+            workers = CB.host_cores()
+            GB = world * B  # the reference's global batch: DataParallel splits it over the GPUs (traintest.py:44-45)
+            it, sub = CB._loader(dict(CB.TRAIN_CONF), GB, workers, 40 * (GB + sub_pad(GB, workers)))
+            if world > 1:
+                torch.manual_seed(1)
+                core = EffNetB2Attention().to(dev).to(memory_format=torch.channels_last)
+                dp = nn.DataParallel(core, device_ids=list(range(world)))
+                dp_opt = torch.optim.Adam(core.parameters(), lr=1e-6, weight_decay=5e-7, betas=(0.95, 0.999))
+                dp_labels = (torch.rand(GB, NCLS, device=dev) < 0.01).float()
+            else:
+                fresh_model()
+            cpu_steps = min(steps, 12 if world == 1 else 6)
 
-        def cpu_step():
-            parts, n = [], 0
-            while n < B:
-                fb, _ = next(it)
-                parts.append(fb)
-                n += fb.shape[0]
-            f = torch.cat(parts)[:B].to(dev, non_blocking=True)  # traintest.py:84
-            return train_step(f)
+            def cpu_step():
+                parts, n = [], 0
+                while n < GB:
+                    fb, _ = next(it)
+                    parts.append(fb)
+                    n += fb.shape[0]
+                f = torch.cat(parts)[:GB].to(dev, non_blocking=True)  # traintest.py:84
+                if world == 1:
+                    return train_step(f)
+                with torch.autocast("cuda", dtype=torch.bfloat16):
+                    out = dp(f)
+                loss = F.binary_cross_entropy(out.float().clamp(1e-7, 1 - 1e-7), dp_labels)
+                dp_opt.zero_grad(set_to_none=True)
+                loss.backward()
+                dp_opt.step()
+                return loss
 
-        res["cpu_loader"], _ = timed(cpu_step, min(steps, 12))
-        res["cpu_loader_workers"] = workers
+            for _ in range(2):
+                cpu_step()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(cpu_steps):
+                loss = cpu_step()
+            loss.item()
+            for i in range(world):
+                torch.cuda.synchronize(i)
+            res["cpu_loader"] = GB * cpu_steps / (time.perf_counter() - t0)
+            res["cpu_loader_workers"] = workers
+            res["cpu_loader_mode"] = "single process" + (f", nn.DataParallel over {world} GPUs, global batch {GB}" if world > 1 else "")
+        barrier()
     if rank == 0:
         os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
         name = "c5.json" if world == 1 else f"c5_n{world}.json"

@@ -15,11 +15,34 @@ using namespace psla;
 
 extern "C" {
 
+// Lane order of one phase.  seed == 0: ascending.  Otherwise a seeded shuffle, different for every phase: between two
+// __syncwarp points the hardware gives no order between the lanes of a warp, so the result must not depend on it -- any
+// lane that read what another lane writes inside the same phase (a shared-memory race: the exchange buffer aliases the
+// staged samples, the power spectra alias the exchange buffer) would show up as a difference between two seeds.
+static void lane_order(unsigned seed, unsigned phase, int (&ord)[32]) {
+    for (int i = 0; i < 32; ++i) ord[i] = i;
+    if (seed == 0) return;
+    unsigned long long s = 0x9E3779B97F4A7C15ull * (seed + 1) + 0xD1B54A32D192ED03ull * (phase + 1);
+    for (int i = 31; i > 0; --i) {
+        s = s * 6364136223846793005ull + 1442695040888963407ull;
+        const int j = static_cast<int>((s >> 33) % static_cast<unsigned>(i + 1));
+        const int t = ord[i];
+        ord[i] = ord[j];
+        ord[j] = t;
+    }
+}
+
 // x: mean-removed (and mixed) waveform, n samples.  out: [m][num_bins] raw log-mel (floor applied).
 // mel_dense: optional [num_bins][256] override (nullptr = native table); window: optional [400] analysis window.
 // force_generic_mel != 0 runs the run-time-loop mel path even when the unrolled one applies.
+int emu_fbank_ordered(const float* x, int n, int num_bins, const float* mel_dense, const float* window, int force_generic_mel,
+                      unsigned order_seed, float* out);
 int emu_fbank(const float* x, int n, int num_bins, const float* mel_dense, const float* window, int force_generic_mel,
               float* out) {
+    return emu_fbank_ordered(x, n, num_bins, mel_dense, window, force_generic_mel, 0u, out);
+}
+int emu_fbank_ordered(const float* x, int n, int num_bins, const float* mel_dense, const float* window, int force_generic_mel,
+                      unsigned order_seed, float* out) {
     if (n < kFrameLen) return -1;
     const int m = 1 + (n - kFrameLen) / kFrameShift;
     std::vector<float> win(kFrameLen), dense(num_bins * 256);
@@ -86,23 +109,30 @@ int emu_fbank(const float* x, int n, int num_bins, const float* mel_dense, const
         }
         cf regs[32][2][16];
         static cf z1[32][32];
-        for (int lane = 0; lane < 32; ++lane) {  // pass 1 (reads the staged samples)
+        int ord[32];
+        const unsigned ph = 8u * static_cast<unsigned>(f0 / kGroupFrames);
+        lane_order(order_seed, ph + 0, ord);
+        for (int li = 0, lane = ord[0]; li < 32; lane = ord[++li < 32 ? li : 0]) {  // pass 1 (reads the staged samples)
             const int h = lane >> 4, n2 = lane & 15;
             pair_pass1(n2, h, par, W.data(), TAB + kTabWin, cmu[2 * h], cmu[2 * h + 1], z1[lane]);
         }
-        for (int lane = 0; lane < 32; ++lane) {  // pass 1 stores (EX aliases the middle of the window)   -- __syncwarp --
+        lane_order(order_seed, ph + 1, ord);
+        for (int li = 0, lane = ord[0]; li < 32; lane = ord[++li < 32 ? li : 0]) {  // pass 1 stores (EX aliases the middle of the window)   -- __syncwarp --
             const int h = lane >> 4, n2 = lane & 15;
             pair_pass1_store(n2, TAB + kTabTwz, EX + h * kExSecondPair, z1[lane]);
         }
-        for (int lane = 0; lane < 32; ++lane) {  // pass 2a (reads)   -- __syncwarp --
+        lane_order(order_seed, ph + 2, ord);
+        for (int li = 0, lane = ord[0]; li < 32; lane = ord[++li < 32 ? li : 0]) {  // pass 2a (reads)   -- __syncwarp --
             const int h = lane & 1, t = lane >> 1;
             pair_pass2_fft(t, EX + h * kExSecondPair, TAB + kTabTw, regs[lane][0], regs[lane][1]);
         }
-        for (int lane = 0; lane < 32; ++lane) {  // pass 2b (P aliases EX) -- __syncwarp --
+        lane_order(order_seed, ph + 3, ord);
+        for (int li = 0, lane = ord[0]; li < 32; lane = ord[++li < 32 ? li : 0]) {  // pass 2b (P aliases EX) -- __syncwarp --
             const int h = lane & 1, t = lane >> 1;
             pair_power_store(t, h, regs[lane][0], regs[lane][1], EX);
         }
-        for (int lane = 0; lane < 32; ++lane) {  // mel                    -- __syncwarp --
+        lane_order(order_seed, ph + 4, ord);
+        for (int li = 0, lane = ord[0]; li < 32; lane = ord[++li < 32 ? li : 0]) {  // mel                    -- __syncwarp --
             float acc[kMelSlots][kGroupFrames];
             if (spec) warp_mel<true>(lane, EX, mt, acc);
             else warp_mel<false>(lane, EX, mt, acc);

@@ -133,3 +133,22 @@ def test_emulated_kernel_zero_input_hits_the_floor(emu):
     assert emu.emu_fbank(_p(x), 1040, 128, None, None, 0, _p(out)) == 5
     assert np.array_equal(out, np.full((5, 128), np.log(np.float32(O.EPS32)), np.float32))
     assert emu.emu_fbank(_p(x), 399, 128, None, None, 0, _p(out)) == -1
+
+
+@pytest.mark.parametrize("generic_mel", [0, 1])
+def test_phases_do_not_depend_on_the_lane_order(emu, generic_mel):
+    """Race check without a GPU tool (compute-sanitizer is closed on the B200 pool): between two __syncwarp points the
+    lanes of a warp run in no defined order, and three shared-memory regions alias each other (staged samples -> exchange
+    buffer -> power spectra).  Stepping every phase in a seeded random lane order must give bit-identical features -- a
+    lane reading inside a phase what another lane writes in the same phase would not."""
+    x = synth_wave(11, 12000, "am")[0].numpy()
+    x = np.ascontiguousarray(x - x.mean(dtype=np.float32))
+    m = 1 + (len(x) - 400) // 160
+    emu.emu_fbank_ordered.argtypes = [F32P, ctypes.c_int, ctypes.c_int, F32P, F32P, ctypes.c_int, ctypes.c_uint, F32P]
+    outs = []
+    for seed in (0, 1, 2, 3, 4):
+        out = np.zeros((m, 128), np.float32)
+        assert emu.emu_fbank_ordered(_p(x), len(x), 128, None, None, generic_mel, seed, _p(out)) == m
+        outs.append(out)
+    for o in outs[1:]:
+        assert np.array_equal(o, outs[0])

@@ -78,7 +78,12 @@ def _check(out, ref, div=STD, tol=TOL, fill=None, near_floor_below=None):
     cell_err = (out - ref).abs() * div
     if near_floor_below is not None:
         at_floor = ref == ((torch.log(torch.tensor(O.EPS32, dtype=torch.float32)) - MEAN) / div)  # exactly log(eps): bit-identical
-        assert torch.equal(out[at_floor], ref[at_floor])
+        # (a cell whose energy equals eps to within rounding may be clamped in one implementation and not in the other:
+        # a handful per 10^7 cells, and those agree to within the tolerance)
+        off = out[at_floor] != ref[at_floor]
+        assert off.sum().item() <= max(0, int(1e-5 * at_floor.sum().item()))
+        if off.any():
+            assert ((out[at_floor] - ref[at_floor]).abs()[off] * div).max().item() <= tol
         near = (ref * div + MEAN <= near_floor_below) & (ref != (fill if fill is not None else float("nan"))) & ~at_floor
         assert near.sum().item() <= 2e-3 * ref.numel()
         assert cell_err[near].max().item() <= 4e-3 if near.any() else True
@@ -144,6 +149,30 @@ def test_ragged_fsd50k_shape(FE):
     fe.close()
 
 
+@pytest.mark.parametrize("B", [24, 96])
+def test_c3_fsd50k_batches_at_recipe_size(FE, B):
+    """C3 at the reference's own batch size (egs/fsd50k/run.sh:21 batch_size=24; 96 = the sweep's next size) and recipe
+    (:24-29 freqm 48, timem 192, mixup 0.5; :60 target_length 3000): clip lengths 0.3 .. 30 s, every other clip mixed with a
+    partner of any length (shorter partners need the statistics pass), int16 PCM input (what the files hold)."""
+    from psla_b200.frontend import to_pcm16
+    fe = FE({**CONF, "target_length": 3000})
+    rng = np.random.default_rng(B)
+    lens = [int(v) for v in rng.integers(4800, 480001, B)]
+    lens[0], lens[1] = 480000, 400
+    waves = [to_pcm16(synth_wave(700 + i, n, ("gauss", "am", "int16")[i % 3])) for i, n in enumerate(lens)]
+    src1 = list(range(B))
+    src2 = [int(rng.integers(0, B)) if rng.random() < 0.5 else -1 for _ in range(B)]
+    lam = [float(rng.beta(10, 10)) if s >= 0 else 0.0 for s in src2]
+    torch.manual_seed(B)
+    masks = [O.draw_mask_offsets(48, 192, 128, 3000) for _ in range(B)]
+    out = fe(waves, src1, src2, lam, masks)
+    assert sum(1 for a, c in zip(src1, src2) if c >= 0 and lens[c] < lens[a]) >= 2  # the statistics kernel ran
+    torch.set_num_threads(max(1, min(16, os.cpu_count() or 1)))
+    ref = O.batch_torch([w.float() / 32768.0 for w in waves], src1, src2, lam, masks, 3000, MEAN, STD)
+    _check(out, ref, fill=_fill(), near_floor_below=-13.0)
+    fe.close()
+
+
 def test_truncation_and_odd_target_length(FE):
     fe = FE({**CONF, "target_length": 77})
     waves = [synth_wave(31, 160000), synth_wave(32, 9000)]
@@ -195,6 +224,115 @@ def test_errors_mirror_the_reference(fe):
     with pytest.raises(PslaError):
         fe(ok, [0], [3], [0.5])
     assert fe(ok, []).shape == (0, 1056, 128)
+    # a descriptor that reaches past the waveform buffer is an error of the call, not an out-of-bounds device read
+    from psla_b200.frontend import PackedWaves
+    buf = synth_wave(1, 16000)[0].cuda()
+    for offs, lens in (([0], [16001]), ([15000], [2000]), ([16000], [400]), ([-4], [4000])):
+        with pytest.raises(PslaError):
+            fe.forward_packed(PackedWaves(buf, np.array(offs, np.int64), np.array(lens, np.int64)), [0])
+    with pytest.raises(PslaError):
+        fe.forward_host(PackedWaves(buf.cpu(), np.array([8000], np.int64), np.array([9000], np.int64)), [0])
+    assert fe.forward_packed(PackedWaves(buf, np.array([15600], np.int64), np.array([400], np.int64)), [0]).shape == (1, 1056, 128)
+
+
+def test_guard_bands_around_every_buffer(fe):
+    """Memory-safety evidence without a tool (compute-sanitizer is closed on this pool): waveforms of awkward lengths at
+    aligned and unaligned offsets are surrounded by NaN (fp32) / full-scale (int16) guard samples, the output is a window of
+    a larger sentinel-filled buffer.  Features equal the oracle's, so no guard sample was ever used (a NaN would spread
+    over its whole frame), and no byte outside the output window was written -- for every descriptor path and layout."""
+    from psla_b200.frontend import PackedWaves, to_pcm16
+    T = 300
+    lens = [400, 401, 559, 560, 561, 1039, 12345, 48000, 47999, 16003]
+    gaps = [0, 1, 2, 3, 4, 5, 7, 9, 13, 64]  # guard samples in front of each waveform: starts at every alignment
+    waves = [synth_wave(500 + i, n, ("gauss", "int16")[i % 2]) for i, n in enumerate(lens)]
+    src1 = list(range(10)) + [7, 8]
+    src2 = [-1, 0, -1, 2, -1, 6, 7, 8, 7, -1, 9, 6]  # longer, shorter and equal partners
+    lam = [0.0, 0.4, 0.0, 0.6, 0.0, 0.5, 0.3, 0.7, 0.45, 0.0, 0.55, 0.35]
+    torch.manual_seed(3)
+    masks = [O.draw_mask_offsets(48, 100, 128, T) for _ in src1]
+    ref = O.batch_torch(waves, src1, src2, lam, masks, T, MEAN, STD)
+    ref16 = O.batch_torch([to_pcm16(w).float() / 32768.0 for w in waves], src1, src2, lam, masks, T, MEAN, STD)
+    for pcm in (False, True):
+        offs, pos = [], 32
+        for g_, n in zip(gaps, lens):
+            pos += g_
+            offs.append(pos)
+            pos += n
+        total = pos + 32
+        if pcm:
+            flat = torch.full((total,), 32767, dtype=torch.int16)
+            for o, w in zip(offs, waves):
+                flat[o:o + w.shape[-1]] = to_pcm16(w)[0]
+        else:
+            flat = torch.full((total,), float("nan"))
+            for o, w in zip(offs, waves):
+                flat[o:o + w.shape[-1]] = w[0]
+        pk = PackedWaves(flat.cuda(), np.array(offs, np.int64), np.array(lens, np.int64))
+        for layout in (("tf", "ft", "ft_bf16") if not fe.exact_clip_mean else ("tf",)):
+            fe.set_output_layout(layout)
+            try:
+                for pmeta in (True, False):
+                    fe.set_param_meta(pmeta)
+                    shape, dtype = fe.out_shape_dtype(len(src1), T)
+                    n_out = int(np.prod(shape))
+                    sentinel = -12345.0 if dtype == torch.float32 else -12352.0
+                    big = torch.full((n_out + 2 * 4096,), sentinel, dtype=dtype, device=fe.device)
+                    out = big[4096:4096 + n_out].view(shape)
+                    fe.forward_packed(pk, src1, src2, lam, masks, out=out, target_length=T)
+                    torch.cuda.synchronize()
+                    assert (big[:4096] == sentinel).all() and (big[4096 + n_out:] == sentinel).all()
+                    got = out.float().cpu() if layout == "tf" else out.float().cpu().transpose(1, 2)
+                    assert not torch.isnan(got).any()
+                    want = ref16 if pcm else ref
+                    tol = TOL if layout != "ft_bf16" else 0.03  # bf16 rounding of values up to ~4
+                    live = want != _fill()
+                    assert ((got - want).abs() * STD)[live].max().item() <= (4e-3 if layout != "ft_bf16" else 0.1) and \
+                        ((got - want).abs() * STD)[live].median().item() <= tol
+            finally:
+                fe.set_output_layout("tf")
+                fe.set_param_meta(True)
+
+
+def test_outlier_samples_do_not_raise_the_noise_floor(fe):
+    """the default clip-mean mode subtracts a per-clip constant instead of the mean.  With the clip's FIRST
+    sample as that constant, a full-scale click at sample 0 in front of a quiet 16-bit body put every staged value at
+    magnitude 0.9 and 1 % of the cells were off by up to 1.2e-2 (mixed clips: lambda * x rounds at ulp(0.9)).  The
+    constant is now a five-sample median of the clip; click, clipped first samples and a loud onset must all stay within
+    the tolerance, mixed and unmixed, fp32 and int16."""
+    from psla_b200.frontend import to_pcm16
+
+    def body(seed, n, amp):  # low-pass noise: nothing but quantisation noise above ~1 kHz
+        g = torch.Generator().manual_seed(seed)
+        x = torch.randn(n + 64, generator=g, dtype=torch.float64)
+        k = torch.hann_window(65, periodic=False, dtype=torch.float64)
+        y = torch.nn.functional.conv1d(x.view(1, 1, -1), (k / k.sum()).view(1, 1, -1)).view(-1)[:n]
+        return (amp * y / y.std()).float().unsqueeze(0)
+
+    n = 80000
+    waves = []
+    for i in range(6):
+        x = body(40 + i, n, 4e-3)
+        if i % 3 == 0:
+            x[0, 0] = 0.9  # click at the very first sample
+        elif i % 3 == 1:
+            x[0, :3] = -1.0  # three clipped samples
+        else:
+            x[0, :1500] += 0.5 * synth_wave(60 + i, 1500, "gauss", amp=0.6)[0].clamp(-1, 1)  # loud onset
+        waves.append(x)
+    src1, src2 = list(range(6)), [1, -1, 3, 0, -1, 4]
+    lam = [0.37, 0.0, 0.61, 0.43, 0.0, 0.29]
+    masks = [(0, 0, 0, 0)] * 6
+    for pcm in (False, True):
+        ws = [to_pcm16(w) for w in waves] if pcm else waves
+        ref_in = [w.float() / 32768.0 for w in ws] if pcm else waves
+        out = fe(ws, src1, src2, lam, masks, target_length=500)
+        ref = O.batch_torch(ref_in, src1, src2, lam, masks, 500, MEAN, STD)
+        ref64 = O.batch_torch(ref_in, src1, src2, lam, masks, 500, MEAN, STD, dtype=torch.float64)
+        live = ref != _fill()
+        err = ((out.cpu() - ref).abs() * STD)[live]
+        ref_err = ((ref.double() - ref64).abs() * STD)[live]
+        assert (err > TOL).sum().item() <= max(3, 2 * int((ref_err > TOL).sum())), ((err > TOL).sum().item(), err.max().item())
+        assert err.max().item() <= max(2e-3, 1.5 * ref_err.max().item())
 
 
 def test_unaligned_offsets_and_shared_buffer(fe):
@@ -499,8 +637,51 @@ def test_c4_long_recording_chunks_equal_per_clip_oracle(FE):
     lr2 = LongRecordingFrontend(fe, x, window_s=10.0, hop_s=2.5)
     f2 = lr2.features(0, len(lr2))
     assert torch.equal(f2[0], got[0]) and torch.equal(f2[4], got[1])  # hop 2.5 s: window 4 starts at 10 s
-    starts, y = lr.predict(lambda f: f.mean(dim=(1, 2)).unsqueeze(1), batch=4)
-    assert y.shape == (7, 1) and starts.tolist() == lr.starts.tolist()
+    pred = lr.predict(lambda f: f.mean(dim=(1, 2)).unsqueeze(1), batch=4, aggregate=None)
+    assert pred.per_window.shape == (7, 1) and pred.starts.tolist() == lr.starts.tolist() and pred.clip is None
+    fe.close()
+
+
+def test_c4_hour_long_recording_end_to_end(FE):
+    """C4 at its real size: one hour of 16 kHz audio = 360 windows of 10 s, features against the oracle window by window,
+    then the whole one-click path -- batched model inference (a stand-in for EffNetAttention: [b, T, 128] -> sigmoid
+    [b, C]) one launch ahead on a second stream, per-window outputs, recording-level mean / max."""
+    from psla_b200.inference import LongRecordingFrontend
+    fe = FE(CONF)
+    g = torch.Generator().manual_seed(7)
+    n = 360 * 160000
+    x = 0.1 * torch.randn(n, generator=g)
+    x[5 * 160000:6 * 160000] *= 0.01   # a quiet window
+    x[100 * 160000:101 * 160000] += 0.3  # a window with a DC offset
+    lr = LongRecordingFrontend(fe, x, window_s=10.0)
+    assert len(lr) == 360
+    feats = torch.cat([f for _, f in lr.batches(128)], dim=0)
+    torch.set_num_threads(max(1, min(16, os.cpu_count() or 1)))
+    chunks = [x[s:s + l].unsqueeze(0) for s, l in zip(lr.starts.tolist(), lr.lengths.tolist())]
+    ref = O.batch_torch(chunks, list(range(360)), [-1] * 360, [0.0] * 360, [(0, 0, 0, 0)] * 360, 1056, MEAN, STD)
+    _check(feats, ref, fill=_fill(), near_floor_below=-13.0)
+    C = 10
+    wgt = torch.randn(128, C, generator=g).to(fe.device) * 0.2
+
+    def model(f):  # time-average -> linear -> sigmoid, returns (output, attention) like EffNetAttention (:146)
+        return torch.sigmoid(f.mean(dim=1) @ wgt), None
+
+    want = torch.sigmoid(feats.mean(dim=1) @ wgt)
+    for batch in (360, 128, 50):
+        pred = lr.predict(model, batch=batch, aggregate="mean")
+        assert torch.allclose(pred.per_window, want, rtol=0, atol=1e-6) and pred.per_window.shape == (360, C)
+        assert torch.allclose(pred.clip, want.mean(0), atol=1e-5)
+    pmax = lr.predict(model, batch=128, aggregate="max")
+    assert torch.equal(pmax.clip, pmax.per_window.max(0).values)
+    top = pmax.top(3, names=[f"class{i}" for i in range(C)])
+    assert len(top) == 3 and top[0][1] >= top[1][1] >= top[2][1] and top[0][0].startswith("class")
+    tl = pred.timeline(0)
+    assert len(tl) == 360 and tl[1][0] == 10.0
+    # a short last window weighs less in the mean
+    lr2 = LongRecordingFrontend(fe, x[:2 * 160000 + 8000], window_s=10.0)
+    p2 = lr2.predict(model, batch=2, aggregate="mean")
+    fr = torch.tensor([998.0, 998.0, 48.0], device=fe.device)
+    assert torch.allclose(p2.clip, (p2.per_window * fr.unsqueeze(1)).sum(0) / fr.sum(), atol=1e-6)
     fe.close()
 
 

@@ -127,3 +127,34 @@ def test_train_configuration_from_files(D, files, gold):
         n_mixed += int((batch.src2 >= 0).sum())
         fl._reap(block=True)
     assert n_mixed > 0
+
+
+def test_staging_buffers_do_not_reuse_memory_of_queued_consumer_work(D, files, gold):
+    """Regression (found by scripts/c5_train.py: NaN weights after the third batch).  The loader copies a batch to the
+    device on a SIDE stream.  Its device buffer must not be a block the caching allocator has just taken back from a
+    main-stream tensor: kernels queued on the main stream may still use that memory, and nothing orders the side-stream
+    copy after them.  Here a long chain of main-stream kernels reads a tensor that is freed while they are still queued;
+    the first batches of a fresh loader are staged right behind it; the chain's result must be unaffected."""
+    from psla_b200.frontend import GpuFbankFrontend
+    conf = json.loads(str(gold["eval_conf"]))
+    fe = GpuFbankFrontend(conf)
+    ds = D.AudiosetDataset(files[0], conf, label_csv=files[1], verbose=False)  # float waveforms: > 1 MB per batch
+    batches = [ds.collate([ds[i] for i in range(16)], pinned=True) for _ in range(3)]
+    nbytes = batches[0].waves.wav.numel() * 4
+    dev = fe.device
+    for rep in range(5):
+        fl = D.FrontendLoader(None, fe)  # fresh: its device buffers are allocated at the first three batches
+        torch.cuda.synchronize()
+        x = torch.ones(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=dev)  # the size the loader will ask for
+        acc = torch.zeros(x.numel(), dtype=torch.int32, device=dev)
+        big = torch.ones(64 << 20, device=dev)
+        for _ in range(60):  # keep the stream busy in front of the reads of x
+            big.mul_(1.0000001)
+        for _ in range(40):
+            acc.add_(x)
+        del x  # back to the allocator while the adds are still queued
+        feats = [fl.features(b).clone() for b in batches]
+        torch.cuda.synchronize()
+        assert int(acc.min()) == 40 and int(acc.max()) == 40, rep
+        assert torch.equal(feats[0], feats[1]) and torch.equal(feats[0], feats[2])
+        _cmp(feats[0], gold["eval_feats"][:16])

@@ -36,6 +36,7 @@
 using namespace psla;
 
 constexpr int kMetaSlots = 4;
+constexpr int kPartialSlots = 3;  // partial-sum buffers of the statistics kernel, rotated: the statistics pass of call k + 1 may run while the streaming kernel of call k still reads its own
 constexpr int kCtasPerSm = 4;  // __launch_bounds__(kThreads, 4): 4 warps x 128 registers and ~53 KB of shared memory per CTA
 constexpr size_t kSmemPerSm = 228 * 1024, kSmemPerCtaReserved = 1024, kSmemPerCtaMax = 227 * 1024;
 
@@ -76,6 +77,7 @@ struct psla_frontend {
         bool pending = false;
     } slots[kMetaSlots];
     int next_slot = 0;
+    int next_partial = 0;
     cudaStream_t copy_stream = nullptr;
     int meta_on_copy_stream = 1;
     // host-side descriptor build buffers; batches of <= kParamClips clips can be passed as kernel parameters
@@ -383,7 +385,7 @@ size_t psla_frontend_workspace_bytes(const psla_frontend_t* h, int n_clips) {
     if (!h || n_clips < 0) return 0;
     const size_t meta = align_up(static_cast<size_t>(n_clips) * sizeof(ClipDesc), 256) +
                         align_up((static_cast<size_t>(n_clips) + 1) * sizeof(ClipCost), 256);
-    return kMetaSlots * meta + static_cast<size_t>(n_clips) * kStatSegs * kStatVals * sizeof(double);
+    return kMetaSlots * meta + kPartialSlots * align_up(static_cast<size_t>(n_clips) * kStatSegs * kStatVals * sizeof(double), 256);
 }
 
 int psla_frontend_noise_roll(psla_frontend_t* h, const float* in, float* out, const float* noise, const float* scale,
@@ -537,7 +539,9 @@ int enqueue_batch(psla_frontend_t* h, const void* wav, bool pcm16, ClipDesc* des
     const bool param_meta = small && h->param_meta;
     ClipDesc* d_desc = nullptr;
     ClipCost* d_cost = nullptr;
-    double* d_part = reinterpret_cast<double*>(static_cast<char*>(workspace) + kMetaSlots * meta_bytes);
+    const size_t part_bytes = align_up(static_cast<size_t>(n_clips) * kStatSegs * kStatVals * sizeof(double), 256);
+    double* d_part = reinterpret_cast<double*>(static_cast<char*>(workspace) + kMetaSlots * meta_bytes + static_cast<size_t>(h->next_partial) * part_bytes);
+    if (any_stats) h->next_partial = (h->next_partial + 1) % kPartialSlots;
     psla_frontend::Slot* slot = nullptr;
     if (!param_meta) {
         const int slot_index = h->next_slot;
@@ -569,21 +573,52 @@ int enqueue_batch(psla_frontend_t* h, const void* wav, bool pcm16, ClipDesc* des
         h->next_slot = (h->next_slot + 1) % kMetaSlots;
     }
 
+    // ---- launch overlap (see psla_frontend_set_launch_overlap in the header) ----
+    // Programmatic stream serialization lets a launch's thread blocks start on SM resources its PREDECESSOR ON THE STREAM
+    // has already left -- if that predecessor signals early, which our kernels do and plain kernels / copies do not (behind
+    // those the attribute changes nothing).  The streaming kernel does not wait before reading its inputs, so the attribute
+    // is only attached when the predecessor is known to be one of our own launches:
+    //   follows_own_launch     the previous chunk of this same forward() call (the library enqueued it a moment ago), or
+    //   PSLA_OVERLAP_STREAM    the caller's promise that nothing that signals early itself sits between two calls.
+    // Further conditions: descriptors in parameter space (no upload in between), output disjoint from those of the
+    // launches that may still run, no tracing / timing.  A statistics pass is part of the chain: it may start behind the
+    // previous call's streaming kernel (own partial-sum buffer), the streaming kernel of THIS call starts behind it and
+    // waits for it only where a clip needs the sums (griddepcontrol.wait in enter_clip).
+    const char* out_lo = reinterpret_cast<const char*>(out);
+    const char* out_hi = out_lo + static_cast<size_t>(n_clips) * target_length * h->nmel * out_elem_bytes(h);
+    bool disjoint = true;
+    for (int i = 0; i < psla_frontend::kPrevOuts; ++i)
+        disjoint = disjoint && (!h->prev_out_lo[i] || out_hi <= h->prev_out_lo[i] || out_lo >= h->prev_out_hi[i]);
+    const bool own_pred = h->prev_valid && h->prev_stream == stream_ && (follows_own_launch || h->pdl == PSLA_OVERLAP_STREAM);
+    const bool chain_ok = h->pdl != PSLA_OVERLAP_OFF && param_meta && !h->trace && !h->timing;
+    const bool overlap_prev_call = chain_ok && own_pred && disjoint;  // the first kernel of this call behind the last one of the previous
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+
     psla_frontend::EvTriple ev{};
     if (h->timing) {
         for (auto& e : ev.e) PSLA_CUDA(h, cudaEventCreate(&e));
         PSLA_CUDA(h, cudaEventRecord(ev.e[0], stream));
     }
     if (any_stats) {
-        const dim3 sg(kStatSegs, n_clips);
+        cudaLaunchConfig_t sc = {};
+        sc.gridDim = dim3(kStatSegs, n_clips);
+        sc.blockDim = dim3(256);
+        sc.dynamicSmemBytes = 0;
+        sc.stream = stream;
+        sc.attrs = attr;
+        sc.numAttrs = overlap_prev_call ? 1 : 0;
         const MetaNone none = {0};
+        cudaError_t se;
         if (param_meta) {
-            if (pcm16) clip_stats_kernel<short, true><<<sg, 256, 0, stream>>>(static_cast<const short*>(wav), nullptr, h->meta_host, d_part, h->exact_mean);
-            else clip_stats_kernel<float, true><<<sg, 256, 0, stream>>>(static_cast<const float*>(wav), nullptr, h->meta_host, d_part, h->exact_mean);
+            if (pcm16) se = cudaLaunchKernelEx(&sc, clip_stats_kernel<short, true>, static_cast<const short*>(wav), static_cast<const ClipDesc*>(nullptr), h->meta_host, d_part, h->exact_mean);
+            else se = cudaLaunchKernelEx(&sc, clip_stats_kernel<float, true>, static_cast<const float*>(wav), static_cast<const ClipDesc*>(nullptr), h->meta_host, d_part, h->exact_mean);
         } else {
-            if (pcm16) clip_stats_kernel<short, false><<<sg, 256, 0, stream>>>(static_cast<const short*>(wav), d_desc, none, d_part, h->exact_mean);
-            else clip_stats_kernel<float, false><<<sg, 256, 0, stream>>>(static_cast<const float*>(wav), d_desc, none, d_part, h->exact_mean);
+            if (pcm16) se = cudaLaunchKernelEx(&sc, clip_stats_kernel<short, false>, static_cast<const short*>(wav), static_cast<const ClipDesc*>(d_desc), none, d_part, h->exact_mean);
+            else se = cudaLaunchKernelEx(&sc, clip_stats_kernel<float, false>, static_cast<const float*>(wav), static_cast<const ClipDesc*>(d_desc), none, d_part, h->exact_mean);
         }
+        PSLA_CUDA(h, se);
         PSLA_CUDA(h, cudaGetLastError());
         h->launches += 1;
     }
@@ -644,21 +679,9 @@ int enqueue_batch(psla_frontend_t* h, const void* wav, bool pcm16, ClipDesc* des
     p.c1 = static_cast<float>(1.0 - static_cast<double>(h->preemph));
     p.cm = h->cm;
     p.trace = h->trace;
-    // Programmatic stream serialization lets this launch's thread blocks start on SM resources its PREDECESSOR ON THE
-    // STREAM has already left -- if that predecessor signals early, which our streaming kernel does and plain kernels /
-    // copies do not (behind those the attribute changes nothing).  This kernel does not wait before reading its
-    // inputs, so the attribute is only attached when the predecessor is known to be one of our own launches:
-    //   follows_own_launch     the previous chunk of this same forward() call (the library enqueued it a moment ago), or
-    //   PSLA_OVERLAP_STREAM    the caller's promise that nothing that signals early itself sits between two calls.
-    // Further conditions: descriptors in parameter space (no upload in between), no statistics kernel in between (its
-    // sums are read at once), output disjoint from those of the launches that may still run, no tracing / timing.
-    const char* out_lo = reinterpret_cast<const char*>(out);
-    const char* out_hi = out_lo + static_cast<size_t>(n_clips) * target_length * h->nmel * out_elem_bytes(h);
-    bool disjoint = true;
-    for (int i = 0; i < psla_frontend::kPrevOuts; ++i)
-        disjoint = disjoint && (!h->prev_out_lo[i] || out_hi <= h->prev_out_lo[i] || out_lo >= h->prev_out_hi[i]);
-    const bool own_pred = h->prev_valid && h->prev_stream == stream_ && (follows_own_launch || h->pdl == PSLA_OVERLAP_STREAM);
-    const bool overlap_ok = h->pdl != PSLA_OVERLAP_OFF && own_pred && param_meta && !any_stats && !h->trace && !h->timing && disjoint;
+    // behind our own statistics kernel the streaming kernel may always start early (it joins it where it needs the sums);
+    // behind the previous call's streaming kernel under the conditions above
+    const bool overlap_ok = any_stats ? chain_ok : overlap_prev_call;
     if (h->prev_stream != stream_)  // ranges written on another stream are ordered by the caller, not by us
         for (int i = 0; i < psla_frontend::kPrevOuts; ++i) h->prev_out_lo[i] = h->prev_out_hi[i] = nullptr;
     h->prev_valid = true;
@@ -674,9 +697,6 @@ int enqueue_batch(psla_frontend_t* h, const void* wav, bool pcm16, ClipDesc* des
     cfg.blockDim = dim3(kThreads);
     cfg.dynamicSmemBytes = h->smem_bytes;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = overlap_ok ? 1 : 0;
     const bool trace = h->trace != nullptr;

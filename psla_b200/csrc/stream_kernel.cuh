@@ -43,7 +43,7 @@ static_assert(sizeof(ClipCost) == 32, "ClipCost layout");
 // measured on B200 (scripts/gpu_trace.py): a live group ~10.3k cycles, a cold start ~+8k, a dead group ~0.3k in a run
 constexpr CostModel kDefaultCost = {64, 2, 48};
 
-constexpr int kStatSegs = 8;  // partial sums per clip
+constexpr int kStatSegs = 32;  // partial sums per clip: one CTA each (8 left the pass latency-bound: 17 us for the 6 clips of an FSD50K batch of 24 that need it)
 constexpr int kStatVals = 3;  // sum(w1), sum(w2), sum(w2[0:min(n1,n2)])
 
 constexpr int kWarpsPerCta = 4;   // four CTAs per SM
@@ -243,10 +243,16 @@ __global__ void __launch_bounds__(256) clip_stats_kernel(const S* __restrict__ w
                                                          const __grid_constant__ std::conditional_t<PMETA, MetaBlock, MetaNone> meta,
                                                          double* __restrict__ partials, int exact) {
     const int b = blockIdx.y, g = blockIdx.x, tid = threadIdx.x;
+    // part of the launch chain (psla_frontend.cu): the streaming kernel behind it may start at once and joins it where a
+    // clip needs these sums; this kernel itself joins ITS predecessor before it exits (stream order stays transitive)
+    pdl_release();
     ClipDesc d;
     if constexpr (PMETA) d = meta.desc[b];
     else d = load_desc(desc + b);
-    if (!(d.flags & kFlagStats)) return;
+    if (!(d.flags & kFlagStats)) {
+        pdl_join();
+        return;
+    }
     // exact == 0 (default clip-mean mode): only the partner's mean is used (enter_clip), the primary waveform is not read
     float s1 = 0.f, s2 = 0.f, s2c = 0.f;
     if (exact) {
@@ -285,6 +291,7 @@ __global__ void __launch_bounds__(256) clip_stats_kernel(const S* __restrict__ w
         for (int w = 0; w < 8; ++w) s += red[w][tid];
         partials[(static_cast<size_t>(b) * kStatSegs + g) * kStatVals + tid] = s;
     }
+    pdl_join();
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -606,12 +613,15 @@ __device__ __forceinline__ void enter_clip(const StreamParams& p, const MS& ms, 
     const int nmin = min(d.n1, d.n2);
     float sub1 = 0.f, mean2 = 0.f, mixmean = 0.f;
     if (d.flags & kFlagStats) {  // whole-clip means from the statistics kernel's partial sums (fixed tree)
+        // the statistics kernel is this launch's predecessor on the stream; when this launch was allowed to start ahead
+        // of its completion, THIS is where it has to be complete and its sums visible (a no-op otherwise)
+        pdl_join();
         const double* ps = p.partials + static_cast<size_t>(b) * kStatSegs * kStatVals;
         double s1 = 0.0, s2 = 0.0, s2c = 0.0;
         if (lane < kStatSegs) {
-            s1 = ps[lane * kStatVals];
-            s2 = ps[lane * kStatVals + 1];
-            s2c = ps[lane * kStatVals + 2];
+            s1 = __ldcg(ps + lane * kStatVals);  // from L2: written by a kernel that may have run concurrently with this one
+            s2 = __ldcg(ps + lane * kStatVals + 1);
+            s2c = __ldcg(ps + lane * kStatVals + 2);
         }
 #pragma unroll
         for (int o = kStatSegs / 2; o > 0; o >>= 1) {
@@ -1065,6 +1075,9 @@ __global__ void __launch_bounds__(kThreads, 4)
                 typename Pcm<S>::reg_t ha[NH], hc[NH];
                 float a0 = 0.f, c0 = 0.f;
                 if (!EXACT) {  // the constant removed from the clip (see mix_sample): a robust level of each waveform
+                    // (costs +0.6 us per 100-clip launch over reading the first sample; measured and rejected in r02:
+                    // prefetching the ten samples into L2 in the prologue, 50.7 vs 49.9 us, and loading them there behind the
+                    // table copy, 50.4 us)
                     a0 = robust_level<S>(m.w1, m.n1);
                     if (m.mix) c0 = robust_level<S>(m.w2, m.nmin);
                 }

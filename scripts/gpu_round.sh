@@ -1,22 +1,20 @@
 #!/bin/bash
-# One gpurun call: GPU parity tests, smoke, bench (both arms), ncu launch list + one full capture of the tile kernel.
+# One gpurun call: GPU parity tests, smoke, bench (both arms, the driver's command line), sweeps, ncu launch list + one full
+# capture of the streaming kernel.  Then: bash scripts/make_profile.sh <tag>
 set -x
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/smi.txt 2>&1
 lscpu | head -20 > gpurun_out/lscpu.txt; nproc >> gpurun_out/lscpu.txt
 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
-tail -5 gpurun_out/pytest_gpu.log
+tail -3 gpurun_out/pytest_gpu.log
 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" >> gpurun_out/smoke.log
-tail -3 gpurun_out/smoke.log
-python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
-cat gpurun_out/bench.json
+tail -2 gpurun_out/smoke.log
+python bench.py --steps 20 --warmup 5 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
+cut -c1-300 gpurun_out/bench.json
 python bench.py --impl reference --steps 5 --warmup 3 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"
-cat gpurun_out/bench_ref.json
-SHORT="python bench.py --steps 6 --warmup 3 --no-cpu-baseline"
-$SHORT > gpurun_out/plain.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $SHORT > gpurun_out/ncu_list.log 2>&1
-echo "ncu list rc=$?"
-$SHORT > gpurun_out/plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:fbank_stream -s 3 -c 2 -f -o gpurun_out/prof_stream $SHORT > gpurun_out/ncu_full.log 2>&1
-echo "ncu full rc=$?"
+cut -c1-300 gpurun_out/bench_ref.json
+python scripts/sweep.py > gpurun_out/sweep.log 2>&1; echo "sweep rc=$?"
+python scripts/layout_bench.py > gpurun_out/layout_bench.log 2>&1; echo "layout rc=$?"; tail -3 gpurun_out/layout_bench.log
+python scripts/parity_report.py gpurun_out/parity.json > gpurun_out/parity.log 2>&1; echo "parity rc=$?"
+bash scripts/gpu_prof.sh
 ls -la gpurun_out

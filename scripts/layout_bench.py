@@ -31,6 +31,7 @@ def main():
     torch.manual_seed(0)
     masks = np.array([P.draw_masks(48, 192, NMEL, T) for _ in range(B)], dtype=np.int32)
     fe = GpuFbankFrontend({"num_mel_bins": NMEL, "target_length": T, "mean": -4.6476, "std": 4.5699}, device=dev)
+    fe.set_launch_overlap("stream")  # back-to-back calls on one stream with nothing in between (like bench.py's value leg)
 
     def timed(step, steps=200):
         for k in range(10):

@@ -530,6 +530,31 @@ def test_overlapping_launches_keep_stream_order(FE):
         torch.cuda.synchronize()
         r1, r2 = (ref_heavy[48:], ref_heavy[:48]) if rep % 2 else (ref_heavy[:48], ref_heavy[48:])
         assert torch.equal(o1, r1) and torch.equal(o2, r2), rep
+    # (c) batches that need the statistics pass (shorter mixup partners): statistics kernel and streaming kernel are one
+    # chain -- the statistics pass of call k + 1 may run behind the streaming kernel of call k (own partial-sum buffer),
+    # the streaming kernel joins it only where a clip needs the sums.  Different batches back to back, rotating buffers.
+    rag = [synth_wave(900 + i, n) for i, n in enumerate((64000, 20000, 48000, 9000, 33000, 64000, 5000, 40000))]
+    pkr = pack_waveforms(rag, device=dev)
+    batches = []
+    for k in range(4):
+        s1 = np.array([(k + i) % 8 for i in range(6)], np.int32)
+        s2 = np.array([(k + 3 * i + 1) % 8 if i % 2 == 0 else -1 for i in range(6)], np.int32)
+        lam = np.full(6, 0.3 + 0.1 * k)
+        batches.append((s1, s2, lam))
+    fe.set_launch_overlap("off")
+    want = [fe.forward_packed(pkr, s1, s2, lam, None, target_length=T).clone() for s1, s2, lam in batches]
+    torch.cuda.synchronize()
+    for mode in ("call", "stream"):
+        fe.set_launch_overlap(mode)
+        outs = [torch.empty(6, T, 128, device=dev) for _ in range(3)]
+        for rep in range(30):
+            got = []
+            for k, (s1, s2, lam) in enumerate(batches):
+                o = outs[(rep + k) % 3]
+                fe.forward_packed(pkr, s1, s2, lam, None, out=o, target_length=T)
+                got.append(o.clone())
+            torch.cuda.synchronize()
+            assert all(torch.equal(g_, w_) for g_, w_ in zip(got, want)), (mode, rep)
 
 
 def test_c2_audioset_train_batch(fe):

@@ -176,11 +176,7 @@ PSLA_HD void pair_pass1_load(int n2, int h, int par, const float* __restrict__ W
         float w[kWinRow];
         static_for<0, kWinRow / 4>([&](auto q_) {
             constexpr int q = decltype(q_)::value;
-#ifdef PSLA_X_NOWIN  // what-if timing build (wrong results): no window loads
-            w[4 * q] = w[4 * q + 1] = w[4 * q + 2] = w[4 * q + 3] = 0.5f;
-#else
             ld4(WINT + kWinRow * n2 + 4 * q, w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
-#endif
         });
         float v[35];
         static_for<0, 35>([&](auto n1_) {
@@ -230,11 +226,7 @@ PSLA_HD void pair_pass2_fft(int t, const float* __restrict__ EX, const float* __
     static_for<0, 8>([&](auto q_) {
         constexpr int n = 2 * decltype(q_)::value;
         float w0r, w0i, w1r, w1i;
-#ifdef PSLA_X_NOTW  // what-if timing build (wrong results): no twiddle loads
-        w0r = 0.6f, w0i = 0.8f, w1r = 0.8f, w1i = -0.6f;
-#else
         ld4(tw + 2 * n, w0r, w0i, w1r, w1i);
-#endif
         if constexpr (n != 0) {  // TW[t][0] == 1
             a[n] = cmul(a[n], w0r, w0i);
             b[n] = cmul_conj(b[n], w0r, w0i);
@@ -266,10 +258,6 @@ PSLA_HD void pair_power_store(int t, int h, const cf (&a)[16], const cf (&b)[16]
         constexpr int ia = brev<4>(k2);              // A[k2]
         constexpr int ib = brev<4>((16 - k2) % 16);  // B[(16-k2) % 16]
         cf u, v;
-#ifdef PSLA_X_NOSEL  // what-if timing build (wrong results in lanes 0, 1): no lane-0 selects
-        u = a[ia];
-        v = b[ib];
-#else
         if constexpr (k2 < 8) {
             u = a[ia];
             constexpr int ia2 = brev<4>((16 - k2) % 16);  // lane 0: A[(16-k2) % 16]
@@ -281,7 +269,6 @@ PSLA_HD void pair_power_store(int t, int h, const cf (&a)[16], const cf (&b)[16]
             u.y = t0 ? b[ib2].y : a[ia].y;
             v = b[ib];
         }
-#endif
         const cf x = cadd(u, conj_(v));  // X = u + conj(v)
         const cf y = csub(u, conj_(v));  // i*Y = u - conj(v)
         const float px = fmaf(x.x, x.x, x.y * x.y);
@@ -306,17 +293,9 @@ template <int R, int OFF>
 PSLA_HD void mel_slot_static(int lane, const float* __restrict__ P, const float* __restrict__ w, int start, float (&acc)[kGroupFrames]) {
     cf a01 = mk(0.f, 0.f), a23 = mk(0.f, 0.f);  // frames (0, 1) and (2, 3): one two-wide FMA each per tap
     const float* p = P + 4 * start;
-#ifdef PSLA_X_MELHALF  // what-if timing build (wrong results): half the taps
-    static_for<0, (R + 1) / 2>([&](auto r_) {
-#else
     static_for<0, R>([&](auto r_) {
-#endif
         constexpr int r = decltype(r_)::value;
-#ifdef PSLA_X_NOMELW  // what-if timing build (wrong results): no weight loads
-        const float wv = 0.25f;
-#else
         const float wv = w[32 * (OFF + r) + lane];
-#endif
         cf p01, p23;
         ld4(p + 4 * r, p01.x, p01.y, p23.x, p23.y);
         a01 = cfma(p01, bc(wv), a01);

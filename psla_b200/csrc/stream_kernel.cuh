@@ -173,11 +173,7 @@ __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefe
 //                  event) -- and because waiting thread blocks keep their SM slots, at most two consecutive launches are
 //                  ever in flight together.  When the launch was not made with the attribute both are no-ops.
 __device__ __forceinline__ void pdl_release() { asm volatile("griddepcontrol.launch_dependents;"); }
-__device__ __forceinline__ void pdl_join() {
-#ifndef PSLA_NO_PDL_WAIT
-    asm volatile("griddepcontrol.wait;" ::: "memory");
-#endif
-}
+__device__ __forceinline__ void pdl_join() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 // Level of a waveform from FIVE samples spread over it (first, quartiles, last): their median.  The default clip-mean mode
 // subtracts this instead of the clip mean (see "Waveform conditioning" below).  One sample would do for the algebra -- any
@@ -315,7 +311,8 @@ constexpr int kNextLive = 1, kNextFull = 2;
 static_assert(CS_END <= kCsWords && CS_SUB1 % 4 == 0 && CS_OFF1 % 4 == 0 && CS_F0 % 4 == 0 && CS_MEFF % 4 == 0 && CS_B % 4 == 0 &&
                   CS_CARRY % 4 == 0 && CS_TR_T0 % 4 == 0 && kWsCS % 4 == 0 && kWarpFloats % 4 == 0,
               "clip-state layout");
-constexpr int kCsMix = 8;  // CS_FLAGS: kFlagAligned1 | kFlagAligned2 | kCsMix
+constexpr int kCsMix = 8;  // CS_FLAGS: kFlagAligned1 | kFlagAligned2 | kCsMix | (number of leading groups with a full window) << kCsFullShift
+constexpr int kCsFullShift = 4;
 
 __device__ __forceinline__ int cs_i(const int* cs, int w) { return *reinterpret_cast<const volatile int*>(cs + w); }
 __device__ __forceinline__ float cs_f(const int* cs, int w) { return __int_as_float(cs_i(cs, w)); }
@@ -355,6 +352,7 @@ struct MixState {
     float mean2;    // EXACT: mean2;  fused: mean2 where the partner is shorter (tail fill)
     float mixmean;  // EXACT only
     int n1, nmin;
+    int gfull1;  // groups [0, gfull1) of the clip can be staged without bounds checks (computed once per clip, enter_clip)
     bool mix, al1, al2;
 };
 
@@ -376,13 +374,20 @@ __device__ __forceinline__ MixState<S> load_mix(const int* cs, const void* wav_)
     m.mix = (fl & kCsMix) != 0;
     m.al1 = (fl & kFlagAligned1) != 0;
     m.al2 = (fl & kFlagAligned2) != 0;
+    m.gfull1 = fl >> kCsFullShift;
     return m;
 }
 
-// the group window [S0, S0 + 880) can be staged without bounds checks
+// the window of group g, [640 g, 640 g + 880), can be staged without bounds checks: it lies inside both waveforms and both
+// are 16-byte aligned
 template <class S>
-__device__ __forceinline__ bool window_full(const MixState<S>& m, int S0) {
-    return m.al1 && S0 + kGroupSamples <= m.n1 && (!m.mix || (m.al2 && S0 + kGroupSamples <= m.nmin));
+__device__ __forceinline__ bool window_full(const MixState<S>& m, int g) {
+    return g < m.gfull1;
+}
+__device__ __forceinline__ int full_groups(int n1, int nmin, bool mix, int flags) {
+    const bool ok = (flags & kFlagAligned1) && (!mix || (flags & kFlagAligned2));
+    const int lim = mix ? nmin : n1;
+    return (ok && lim >= kGroupSamples) ? (lim - kGroupSamples) / kStepSamples + 1 : 0;
 }
 
 template <bool FULL, class S>
@@ -447,6 +452,20 @@ __device__ __forceinline__ void stage_issue(const MixState<S>& m, int S0, int la
                                             typename Pcm<S>::reg_t (&c)[NIT]) {
     using Geo = StageGeom<U0, U1>;
     static_assert(NIT >= Geo::kIters, "register arrays too small");
+    if (FULL && Geo::kFloat4 % 32 == 0) {  // whole iterations, no bounds: one base pointer per waveform, immediate offsets
+        const S* p1 = m.w1 + (S0 + U0 + 4 * lane);
+#pragma unroll
+        for (int it = 0; it < Geo::kIters; ++it) a[it] = Pcm<S>::load_vec(p1 + 128 * it);
+        if (m.mix) {
+            const S* p2 = m.w2 + (S0 + U0 + 4 * lane);
+#pragma unroll
+            for (int it = 0; it < Geo::kIters; ++it) c[it] = Pcm<S>::load_vec(p2 + 128 * it);
+        } else {
+#pragma unroll
+            for (int it = 0; it < Geo::kIters; ++it) c[it] = Pcm<S>::zero();
+        }
+        return;
+    }
 #pragma unroll
     for (int it = 0; it < Geo::kIters; ++it) {
         const int L = lane + 32 * it;
@@ -492,10 +511,8 @@ __device__ __forceinline__ void stage_commit(const MixState<S>& m, int S0, int l
         carry = __shfl_sync(0xffffffffu, x.w, 31);
         last_w = x.w;
         float s4 = (x.x + x.y) + (x.z + x.w);
-#ifndef PSLA_X_NOBS  // what-if timing build (wrong results): block sums not reduced
         s4 += __shfl_xor_sync(0xffffffffu, s4, 1);
         s4 += __shfl_xor_sync(0xffffffffu, s4, 2);
-#endif
         if (in) {
             float4 dd;
             dd.x = fmaf(-pe, prev, x.x);
@@ -510,6 +527,8 @@ __device__ __forceinline__ void stage_commit(const MixState<S>& m, int S0, int l
             else if (u_first >= kStepSamples) dst = p_hi + u;
             else if (u_first >= 320 && u_last < kStepSamples) dst = p_mid + 16 + u;
             else if (u_first >= kOverlapSamples && u_last < 320) dst = p_mid + u;
+            else if (u_first >= kOverlapSamples && u_last < kStepSamples) dst = p_mid + u + (u >= 320 ? 16 : 0);  // straddles the padding
+            else if (u_first >= 320 && u_first < kStepSamples) dst = (u < kStepSamples) ? p_mid + 16 + u : p_hi + u;  // straddles 640
             else dst = (u < kOverlapSamples) ? p_lo + u : (u < kStepSamples ? p_mid + u + (u >= 320 ? 16 : 0) : p_hi + u);
             *reinterpret_cast<float4*>(dst) = dd;
             if ((lane & 3) == 0) {
@@ -648,7 +667,7 @@ __device__ __forceinline__ void enter_clip(const StreamParams& p, const MS& ms, 
     if (lane == 0) {
         cs_set_q(cs, CS_N1, d.n1, nmin, __float_as_int(mix ? d.l1 : 1.0f), __float_as_int(mix ? d.l2 : 0.0f));
         cs_set_q(cs, CS_SUB1, __float_as_int(sub1), __float_as_int(mean2), __float_as_int(mixmean),
-                 (d.flags & (kFlagAligned1 | kFlagAligned2)) | (mix ? kCsMix : 0));
+                 (d.flags & (kFlagAligned1 | kFlagAligned2)) | (mix ? kCsMix : 0) | (full_groups(d.n1, nmin, mix, d.flags) << kCsFullShift));
         cs_set_q(cs, CS_OFF1, static_cast<int>(d.off1), static_cast<int>(d.off1 >> 32), static_cast<int>(d.off2), static_cast<int>(d.off2 >> 32));
         cs_set_q(cs, CS_F0, d.f0, d.f1, d.t0, d.t1);
         cs_set_q(cs, CS_MEFF, d.m_eff, cc.a_lo, cc.a_hi, cc.b_lo);
@@ -1067,7 +1086,7 @@ __global__ void __launch_bounds__(kThreads, 4)
         {
             MixState<S> m = load_mix<S>(cs, p.wav);
             const int S0 = g * kStepSamples;
-            const bool full = window_full(m, S0);
+            const bool full = window_full(m, g);
             const int par = g & 1;
             float carry;
             if (!staged) {  // cold start of a run of groups: the whole window is loaded here, nothing was prefetched
@@ -1104,7 +1123,7 @@ __global__ void __launch_bounds__(kThreads, 4)
             if (TRACE && p.trace) trace_phase(p, cs, lane, 5);
             budget -= p.cm.live + (run_start(dq.y, dq.z, g) ? p.cm.cold : 0);
             next_live = (g + 1 < p.G) && !is_dead(dq.y, dq.z, dq.w, g + 1) && budget > 0;
-            const bool full_next = next_live && window_full(m, (g + 1) * kStepSamples);
+            const bool full_next = next_live && window_full(m, g + 1);
             gn = (g << 2) | (next_live ? kNextLive : 0) | (full_next ? kNextFull : 0);
             if (lane == 0) cs[CS_CARRY] = __float_as_int(carry);
         }

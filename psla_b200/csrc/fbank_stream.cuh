@@ -101,6 +101,9 @@ constexpr int kXsFloats = 8;   // (1-p) * x at u = 0, 160, 320, 480 (per parity;
 // Exchange buffer of one frame pair, organised by the ROW PAIRS pass 2 consumes: EX[t][n2] = (Z1[ka][n2], Z1[kb][n2]) with
 // ka = t, kb = 32 - t (t = 0: rows 0 and 16) -- 16 bytes per (t, n2), so pass 1 stores and pass 2 loads are all 128-bit.
 // Row stride 68 floats: the 8 lanes of a quarter-warp (4 consecutive t x 2 pairs) read 8 distinct 16-byte bank groups.
+// (The compiler spends ~45 MOVs per group on bringing the four registers of each 128-bit store together.  Storing the
+// two rows in separate arrays with 64-bit stores -- no MOVs, same wavefronts, conflict-free -- was measured in r02:
+// 50.1 instead of 48.2 us per launch; twice the store instructions through the memory-instruction queue cost more.)
 constexpr int kExRowFloats = 68;
 constexpr int kExPairFloats = 16 * kExRowFloats;  // 1088 floats = 4352 B
 constexpr int kTwRowFloats = 36;                  // row stride of the inter-pass twiddle table TW[t][n2]

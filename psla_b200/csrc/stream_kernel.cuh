@@ -299,7 +299,7 @@ __global__ void __launch_bounds__(256) clip_stats_kernel(const S* __restrict__ w
 enum ClipStateWord {
     CS_N1 = 0, CS_NMIN, CS_L1, CS_L2,                                    // quad 0: conditioning
     CS_SUB1, CS_MEAN2, CS_MIXMEAN, CS_FLAGS,                             // quad 1: conditioning
-    CS_OFF1 /* 2 words */, CS_OFF1_HI, CS_OFF2 /* 2 words */, CS_OFF2_HI,  // quad 2: waveform offsets
+    CS_OFF1 /* 2 words */, CS_OFF1_HI, CS_OFF2 /* 2 words */, CS_OFF2_HI,  // quad 2: waveform addresses
     CS_F0, CS_F1, CS_T0, CS_T1,                                          // quad 3: masks
     CS_MEFF, CS_ALO, CS_AHI, CS_BLO,                                     // quad 4: live rows / dead group ranges
     // loop state of the warp (same reason: nothing may stay live in registers across the FFT phases)
@@ -362,8 +362,9 @@ __device__ __forceinline__ MixState<S> load_mix(const int* cs, const void* wav_)
     MixState<S> m;
     const int4 q0 = cs_q(cs, CS_N1), q1 = cs_q(cs, CS_SUB1), q2 = cs_q(cs, CS_OFF1);
     const int fl = q1.w;
-    m.w1 = wav + ((static_cast<long long>(q2.y) << 32) | static_cast<unsigned>(q2.x));
-    m.w2 = wav + ((static_cast<long long>(q2.w) << 32) | static_cast<unsigned>(q2.z));
+    (void)wav;  // quad 2 holds the waveforms' ADDRESSES (enter_clip adds the buffer base once per clip, not twice per step)
+    m.w1 = reinterpret_cast<const S*>((static_cast<unsigned long long>(static_cast<unsigned>(q2.y)) << 32) | static_cast<unsigned>(q2.x));
+    m.w2 = reinterpret_cast<const S*>((static_cast<unsigned long long>(static_cast<unsigned>(q2.w)) << 32) | static_cast<unsigned>(q2.z));
     m.n1 = q0.x;
     m.nmin = q0.y;
     m.l1 = __int_as_float(q0.z);
@@ -497,7 +498,7 @@ __device__ __forceinline__ void stage_commit(const MixState<S>& m, int S0, int l
     float* p_lo = WS + kWsOV + par * kOvFloats;                // u < 240
     float* p_mid = WS + kWsDM - kOverlapSamples;               // 240 <= u < 640 (+ 16 from u = 320 on)
     float* p_hi = WS + kWsOV + (par ^ 1) * kOvFloats - kStepSamples;  // u >= 640
-    float last_w = 0.f;
+    float last_w = carry;
 #pragma unroll
     for (int it = 0; it < Geo::kIters; ++it) {
         const int L = lane + 32 * it;
@@ -506,9 +507,9 @@ __device__ __forceinline__ void stage_commit(const MixState<S>& m, int S0, int l
         const bool in = ((it + 1) * 32 <= Geo::kFloat4) || L < Geo::kFloat4;
         const float4 fa = Pcm<S>::to_float4(a[it]), fc = Pcm<S>::to_float4(c[it]);
         const float4 x = mix4<EXACT, FULL>(m, fa, fc, s);
-        float prev = __shfl_up_sync(0xffffffffu, x.w, 1);
-        if (lane == 0) prev = carry;
-        carry = __shfl_sync(0xffffffffu, x.w, 31);
+        // the pre-emphasis neighbour x[u - 1]: lane l - 1's last sample of THIS iteration, for lane 0 lane 31's last sample
+        // of the PREVIOUS one (the incoming carry at first) -- one rotating shuffle: lane 31 sends the older value
+        const float prev = __shfl_sync(0xffffffffu, lane == 31 ? last_w : x.w, (lane + 31) & 31);
         last_w = x.w;
         float s4 = (x.x + x.y) + (x.z + x.w);
         s4 += __shfl_xor_sync(0xffffffffu, s4, 1);
@@ -544,7 +545,7 @@ __device__ __forceinline__ void stage_commit(const MixState<S>& m, int S0, int l
             }
         }
     }
-    if (Geo::kLastLane != 31) carry = __shfl_sync(0xffffffffu, last_w, Geo::kLastLane);
+    carry = __shfl_sync(0xffffffffu, last_w, Geo::kLastLane);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -624,7 +625,7 @@ __device__ __forceinline__ void warp_fill(float* __restrict__ ptr, long long cou
 }
 
 // load a clip's descriptor, derive its conditioning constants, park everything in the warp's clip-state words
-template <bool EXACT, class MS>
+template <bool EXACT, class S, class MS>
 __device__ __forceinline__ void enter_clip(const StreamParams& p, const MS& ms, int b, int lane, int* cs) {
     const ClipDesc d = ms.desc(b);
     const ClipCost cc = ms.cost(b);
@@ -668,7 +669,9 @@ __device__ __forceinline__ void enter_clip(const StreamParams& p, const MS& ms, 
         cs_set_q(cs, CS_N1, d.n1, nmin, __float_as_int(mix ? d.l1 : 1.0f), __float_as_int(mix ? d.l2 : 0.0f));
         cs_set_q(cs, CS_SUB1, __float_as_int(sub1), __float_as_int(mean2), __float_as_int(mixmean),
                  (d.flags & (kFlagAligned1 | kFlagAligned2)) | (mix ? kCsMix : 0) | (full_groups(d.n1, nmin, mix, d.flags) << kCsFullShift));
-        cs_set_q(cs, CS_OFF1, static_cast<int>(d.off1), static_cast<int>(d.off1 >> 32), static_cast<int>(d.off2), static_cast<int>(d.off2 >> 32));
+        const unsigned long long a1 = reinterpret_cast<unsigned long long>(static_cast<const S*>(p.wav) + d.off1);
+        const unsigned long long a2 = reinterpret_cast<unsigned long long>(static_cast<const S*>(p.wav) + d.off2);
+        cs_set_q(cs, CS_OFF1, static_cast<int>(a1), static_cast<int>(a1 >> 32), static_cast<int>(a2), static_cast<int>(a2 >> 32));
         cs_set_q(cs, CS_F0, d.f0, d.f1, d.t0, d.t1);
         cs_set_q(cs, CS_MEFF, d.m_eff, cc.a_lo, cc.a_hi, cc.b_lo);
     }
@@ -712,6 +715,15 @@ __device__ __forceinline__ void epilogue(const StreamParams& p, const int* cs, c
         lb[i] = keep[i] ? p.log_bias : fill;
     }
     const int rows = min(kGroupFrames, p.T - f0);
+    if (FASTLOG && NMEL != 0 && f0 + kGroupFrames <= min(m_eff, p.T) && (f0 + kGroupFrames <= t0 || f0 >= t1)) {
+        // all four rows carry features (the common case): no row selects, no row predicates
+#pragma unroll
+        for (int q = 0; q < kGroupFrames; ++q) {
+#pragma unroll
+            for (int i = 0; i < kMelSlots; ++i) __stcs(col[i] + q * nmel, fmaf(lg2_ftz(fmaxf(acc[i][q], eps)), la[i], lb[i]));
+        }
+        return;
+    }
     if (FASTLOG) {
         // straight-line: 16 independent cells (their MUFU / FMA latencies overlap), rows that are padding or time-masked by
         // a select, rows past target_length by predicated stores -- no branch fences the scheduler
@@ -1054,7 +1066,7 @@ __global__ void __launch_bounds__(kThreads, 4)
     while (true) {
         if (b >= p.n_clips || budget <= 0) break;
         if (b != loaded_b) {
-            enter_clip<EXACT>(p, ms, b, lane, cs);
+            enter_clip<EXACT, S>(p, ms, b, lane, cs);
             loaded_b = b;
             staged = false;
             if (TRACE && p.trace) trace_phase(p, cs, lane, 4);
@@ -1122,7 +1134,8 @@ __global__ void __launch_bounds__(kThreads, 4)
             else stage_commit<EXACT, kOverlapSamples, kGroupSamples, false>(m, S0, lane, p.preemph, p.c1, ra, rc, WS, par, carry);
             if (TRACE && p.trace) trace_phase(p, cs, lane, 5);
             budget -= p.cm.live + (run_start(dq.y, dq.z, g) ? p.cm.cold : 0);
-            next_live = (g + 1 < p.G) && !is_dead(dq.y, dq.z, dq.w, g + 1) && budget > 0;
+            // (g is live: it lies in [0, a_lo) or in [a_hi, b_lo); the run it belongs to ends at a_lo or at b_lo <= G)
+            next_live = g + 1 < (g < dq.y ? dq.y : dq.w) && budget > 0;
             const bool full_next = next_live && window_full(m, g + 1);
             gn = (g << 2) | (next_live ? kNextLive : 0) | (full_next ? kNextFull : 0);
             if (lane == 0) cs[CS_CARRY] = __float_as_int(carry);

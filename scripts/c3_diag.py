@@ -1,5 +1,5 @@
 import os, sys, time, numpy as np, torch
-sys.path.insert(0, '/root/repo')
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from psla_b200 import params as P
 from psla_b200.frontend import GpuFbankFrontend, PackedWaves
 dev = torch.device('cuda', 0)

@@ -1,5 +1,5 @@
 import os, sys, tempfile, torch, numpy as np
-sys.path.insert(0, '/root/repo'); sys.path.insert(0, '/root/repo/scripts')
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, 'scripts'))
 import loader_bench as LB
 from psla_b200 import params as P
 from psla_b200.dataloaders import AudiosetDataset, FrontendLoader, pcm16_lazy_loader

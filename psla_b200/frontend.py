@@ -64,6 +64,8 @@ def pack_waveforms(waves: Sequence[torch.Tensor], device: Union[str, torch.devic
             w = w.materialize()
         w = w.detach()
         w = w[0] if w.dim() == 2 else w
+        if dtype == torch.float32 and w.dtype == torch.int16:  # a batch that mixes decoded floats and 16-bit PCM: the
+            w = w.to(torch.float32) / 32768.0                  # decoder's normalisation (torchaudio.load: value / 32768)
         flat[starts[i]:starts[i] + lens[i]] = w.to(dtype)
     if device is not None:
         flat = flat.to(device, non_blocking=pinned)

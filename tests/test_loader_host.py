@@ -94,3 +94,14 @@ def test_pooled_collate_packs_into_shared_slots(files, golden_dir):
     small = PinnedSlotPool(1, 64, torch.int16, register=False)
     b = AudiosetDataset.collate([ds[0], ds[1]], pinned=False, pool=small)
     assert b.slot == -1 and b.waves.wav is not None and small.free.get(timeout=1) == 0
+
+
+def test_batches_mixing_pcm_and_float_waveforms_use_the_decoder_scale():
+    """A 16-bit file next to one the float decoder handled (pcm16_loader falls back for other encodings): the packed batch
+    is fp32 and the int16 samples are normalised like torchaudio.load does (value / 32768), not copied as raw integers."""
+    a = torch.tensor([[100, -200, 32767, -32768, 5]], dtype=torch.int16)
+    b = torch.tensor([[0.25, -0.5, 0.125]])
+    p = pack_waveforms([a, b])
+    assert p.wav.dtype == torch.float32
+    assert torch.equal(p.wav[:5], a[0].float() / 32768.0) and torch.equal(p.wav[8:11], b[0])
+    assert pack_waveforms([a, a]).wav.dtype == torch.int16

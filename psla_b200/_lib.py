@@ -15,25 +15,28 @@ PSLA_OK = 0
 STATUS_NAMES = {0: "PSLA_OK", -1: "PSLA_E_INVALID", -2: "PSLA_E_UNSUPPORTED", -3: "PSLA_E_SHORT_CLIP",
                 -4: "PSLA_E_MASK", -5: "PSLA_E_WORKSPACE", -6: "PSLA_E_CUDA", -7: "PSLA_E_NOMEM"}
 
-# every symbol include/psla_frontend.h declares: name -> (restype, argtypes)
+# every symbol include/psla_frontend.h declares: name -> (restype, argtypes).  The host metadata arrays of the forward entry
+# points (int64 / int32 / double pointers in the header) are bound as void*: the caller passes the numpy buffers' addresses as
+# plain integers, which costs 1 us per array instead of the 2.7 us of `ndarray.ctypes.data_as(POINTER(...))` -- six arrays
+# per call next to a 48 us kernel.
 SYMBOLS = {
     "psla_frontend_create": (c_int, [POINTER(c_void_p), c_int, c_int, c_int, c_float, c_float, c_float, c_float, c_float]),
     "psla_frontend_destroy": (None, [c_void_p]),
     "psla_frontend_set_tables": (c_int, [c_void_p, c_void_p, c_void_p]),
     "psla_frontend_get_tables": (c_int, [c_void_p, c_void_p, c_void_p]),
     "psla_frontend_workspace_bytes": (c_size_t, [c_void_p, c_int]),
-    "psla_frontend_forward": (c_int, [c_void_p, c_void_p, c_int64, POINTER(c_int64), POINTER(c_int64), c_int, POINTER(c_int32), POINTER(c_int32),
-                                      POINTER(c_double), POINTER(c_int32), c_int, c_int, c_float, c_float, c_int,
+    "psla_frontend_forward": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
+                                      c_void_p, c_void_p, c_int, c_int, c_float, c_float, c_int,
                                       c_void_p, c_void_p, c_size_t, c_void_p]),
-    "psla_frontend_forward_host": (c_int, [c_void_p, c_void_p, c_int64, POINTER(c_int64), POINTER(c_int64), c_int, POINTER(c_int32), POINTER(c_int32),
-                                           POINTER(c_double), POINTER(c_int32), c_int, c_int, c_float, c_float, c_int,
+    "psla_frontend_forward_host": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
+                                           c_void_p, c_void_p, c_int, c_int, c_float, c_float, c_int,
                                            c_void_p, c_void_p]),
     "psla_frontend_device_out": (c_void_p, [c_void_p]),
-    "psla_frontend_forward_pcm16": (c_int, [c_void_p, c_void_p, c_int64, POINTER(c_int64), POINTER(c_int64), c_int, POINTER(c_int32), POINTER(c_int32),
-                                            POINTER(c_double), POINTER(c_int32), c_int, c_int, c_float, c_float, c_int,
+    "psla_frontend_forward_pcm16": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
+                                            c_void_p, c_void_p, c_int, c_int, c_float, c_float, c_int,
                                             c_void_p, c_void_p, c_size_t, c_void_p]),
-    "psla_frontend_forward_host_pcm16": (c_int, [c_void_p, c_void_p, c_int64, POINTER(c_int64), POINTER(c_int64), c_int, POINTER(c_int32),
-                                                 POINTER(c_int32), POINTER(c_double), POINTER(c_int32), c_int, c_int, c_float, c_float,
+    "psla_frontend_forward_host_pcm16": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int, c_void_p,
+                                                 c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_float,
                                                  c_int, c_void_p, c_void_p]),
     "psla_frontend_noise_roll": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, POINTER(c_float), POINTER(c_int32), c_int, c_int,
                                          ctypes.c_uint64, c_void_p]),

@@ -77,11 +77,21 @@ def to_pcm16(wave: torch.Tensor) -> torch.Tensor:
     return torch.clamp(torch.round(wave.to(torch.float32) * 32768.0), -32768, 32767).to(torch.int16)
 
 
-def _as_c(arr: Optional[np.ndarray], dtype, ctype):
+def _raw_stream(device: torch.device) -> int:
+    """cudaStream_t of torch's current stream on `device` as an integer (the private fast path when it exists: the public
+    accessor builds a Stream object per call)."""
+    try:
+        return torch._C._cuda_getCurrentRawStream(device.index)
+    except AttributeError:  # pragma: no cover
+        return torch.cuda.current_stream(device).cuda_stream
+
+
+def _as_c(arr: Optional[np.ndarray], dtype, ctype=None):
+    """(contiguous array of `dtype` -- keep it alive across the call --, its address as an int for a void* argument)."""
     if arr is None:
         return None, None
     a = np.ascontiguousarray(arr, dtype=dtype)
-    return a, a.ctypes.data_as(ctypes.POINTER(ctype))
+    return a, a.ctypes.data
 
 
 class GpuFbankFrontend:
@@ -236,7 +246,9 @@ class GpuFbankFrontend:
         return win, mel
 
     def _workspace(self, n_clips: int) -> torch.Tensor:
-        need = int(self.lib.psla_frontend_workspace_bytes(self._h, n_clips))
+        need = self._ws.get(n_clips)
+        if need is None:
+            need = self._ws[n_clips] = int(self.lib.psla_frontend_workspace_bytes(self._h, n_clips))
         ws = self._ws.get("buf")
         if ws is None or ws.numel() < need:
             ws = torch.empty(max(need, 1 << 16), dtype=torch.uint8, device=self.device)
@@ -266,7 +278,7 @@ class GpuFbankFrontend:
         al, pl = _as_c(None if lam is None else np.asarray(lam), np.float64, ctypes.c_double)
         am, pm = _as_c(None if masks is None else np.asarray(masks).reshape(B, 4), np.int32, ctypes.c_int32)
         ws = self._workspace(B)
-        stream = torch.cuda.current_stream(self.device).cuda_stream
+        stream = _raw_stream(self.device)
         if wav.dtype not in (torch.float32, torch.int16):
             raise ValueError("waveforms must be float32 or int16 PCM")
         fwd = self.lib.psla_frontend_forward_pcm16 if wav.dtype == torch.int16 else self.lib.psla_frontend_forward

@@ -47,12 +47,12 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return BUILT_LIB
 
 
-def build_variant(name: str, defines=(), slim: bool = True, verbose: bool = False) -> str:
+def build_variant(name: str, defines=(), slim: bool = True, verbose: bool = False, extra_flags=()) -> str:
     """Experimental build csrc/variants/libpsla_<name>.so with extra -D flags.  slim: only the kernels the bench batch uses
     (-DPSLA_SLIM: default clip-mean mode, 128 mel bins, fp32 samples, [B, T, F] output) -- seconds instead of minutes."""
     os.makedirs(VARIANT_DIR, exist_ok=True)
     out = os.path.join(VARIANT_DIR, f"libpsla_{name}.so")
-    cmd = [_nvcc(), *NVCC_FLAGS, *(["-DPSLA_SLIM"] if slim else []), *[f"-D{d}" for d in defines], "-Xptxas", "-v", "-o", out, *SOURCES]
+    cmd = [_nvcc(), *NVCC_FLAGS, *(["-DPSLA_SLIM"] if slim else []), *[f"-D{d}" for d in defines], *extra_flags, "-Xptxas", "-v", "-o", out, *SOURCES]
     res = subprocess.run(cmd, cwd=CSRC, capture_output=True, text=True)
     if res.returncode != 0:
         raise RuntimeError(f"nvcc failed for variant {name}:\n" + res.stdout + res.stderr)

@@ -12,8 +12,10 @@ from psla_b200 import build  # noqa: E402
 
 
 def one(spec):
-    name, _, defs = spec.partition(":")
-    path = build.build_variant(name, [d for d in defs.split(",") if d])
+    name, _, defs = spec.partition(":")  # name:DEF1,DEF2  -- an entry starting with '-' is passed to nvcc as a flag (use ';' for ',')
+    items = [d for d in defs.split(",") if d]
+    path = build.build_variant(name, [d for d in items if not d.startswith("-")],
+                               extra_flags=[f.replace(";", ",") for d in items if d.startswith("-") for f in d.split(" ")])
     regs = [ln.strip() for ln in open(path + ".ptxas.txt") if "registers" in ln or "spill" in ln]
     return name, path, regs
 

@@ -167,11 +167,16 @@ class PinnedSlotPool:
     dataloader worker takes a free slot, packs its batch into it (plain memory writes -- workers never touch CUDA), and the
     main process DMAs straight out of it.  Create it BEFORE the DataLoader starts its workers (they inherit it)."""
 
-    def __init__(self, n_slots: int, slot_samples: int, dtype: torch.dtype = torch.int16, register: Optional[bool] = None):
+    def __init__(self, n_slots: int, slot_samples: int, dtype: torch.dtype = torch.int16, register: Optional[bool] = None,
+                 label_floats: int = 0):
         import torch.multiprocessing as mp
 
         self.n_slots, self.slot_samples, self.dtype = int(n_slots), int(slot_samples), dtype
         self.buf = torch.zeros((self.n_slots, self.slot_samples), dtype=dtype).share_memory_()
+        # the batch's label matrix travels in the slot too: a torch tensor sent through the DataLoader's queue costs a
+        # round trip to the worker's file-descriptor server (0.5 ms per batch on the main thread, measured)
+        self.label_floats = int(label_floats)
+        self.labels = torch.zeros((self.n_slots, max(self.label_floats, 1)), dtype=torch.float32).share_memory_()
         self.free = mp.get_context(mp.get_start_method(allow_none=True) or "fork").Queue()
         for i in range(self.n_slots):
             self.free.put(i)
@@ -181,7 +186,8 @@ class PinnedSlotPool:
         if register:
             torch.cuda.init()
             err = torch.cuda.cudart().cudaHostRegister(self.buf.data_ptr(), self.buf.numel() * self.buf.element_size(), 0)
-            self.registered = int(err) == 0
+            err2 = torch.cuda.cudart().cudaHostRegister(self.labels.data_ptr(), self.labels.numel() * 4, 0)
+            self.registered = int(err) == 0 and int(err2) == 0
         self._owner_pid = __import__("os").getpid()
 
     def view(self, slot: int, n: int) -> torch.Tensor:
@@ -200,6 +206,7 @@ class PinnedSlotPool:
         try:
             if self.registered and __import__("os").getpid() == self._owner_pid:
                 torch.cuda.cudart().cudaHostUnregister(self.buf.data_ptr())
+                torch.cuda.cudart().cudaHostUnregister(self.labels.data_ptr())
         except Exception:
             pass
 
@@ -227,6 +234,7 @@ class RawBatch:
     noise: Optional[torch.Tensor] = None  # [B, T, F] host-drawn fields (pinned), or None: the kernel draws them
     conf: Optional[tuple] = None  # (num_mel_bins, target_length, mean, std, skip_norm)
     slot: int = -1  # PinnedSlotPool slot holding the waveforms (waves.wav is then resolved by the FrontendLoader)
+    labels_shape: Optional[tuple] = None  # set when the labels sit in the slot as well (`labels` is then None in transit)
 
     def __len__(self):
         return len(self.src1)
@@ -236,7 +244,8 @@ class RawBatch:
         w = self.waves
         if w.wav is not None and not w.wav.is_pinned():
             self.waves = PackedWaves(w.wav.pin_memory(), w.offsets, w.lengths)
-        self.labels = self.labels.pin_memory()
+        if self.labels is not None:
+            self.labels = self.labels.pin_memory()
         if self.noise is not None:
             self.noise = self.noise.pin_memory()
         return self
@@ -378,9 +387,15 @@ class AudiosetDataset(Dataset):
         packed = pack_waveforms(waves, device=None, pinned=pinned, out=dst)
         if slot >= 0:  # the main process has the same mapping: only the slot index travels
             packed = PackedWaves(None, packed.offsets, packed.lengths)
+        labels, labels_shape = None, None
+        if slot >= 0 and items and len(items) * items[0].labels.numel() <= pool.label_floats:
+            labels_shape = (len(items), items[0].labels.numel())
+            torch.stack([it.labels for it in items], out=pool.labels[slot, :labels_shape[0] * labels_shape[1]].view(labels_shape))
+        else:
+            labels = torch.stack([it.labels for it in items])
         batch = RawBatch(packed, np.array(src1, np.int32), np.array(src2, np.int32), np.array(lam, np.float64),
-                         np.array(masks, np.int32).reshape(-1, 4), torch.stack([it.labels for it in items]),
-                         conf=items[0].conf if items else None, slot=slot)
+                         np.array(masks, np.int32).reshape(-1, 4), labels, conf=items[0].conf if items else None, slot=slot,
+                         labels_shape=labels_shape)
         if any(getattr(it.params, "noise", False) for it in items):
             batch.noise_scale = np.array([it.params.noise_scale for it in items], np.float64)
             batch.roll = np.array([it.params.roll for it in items], np.int32)
@@ -456,7 +471,7 @@ class FrontendLoader:
         # free slot -- so the pool has to be larger than everything that can be in flight, or the loader deadlocks.
         in_flight = max(1, num_workers) * (prefetch_factor or 2)
         n_slots = max(pool_slots or 0, in_flight + 3)
-        pool = PinnedSlotPool(n_slots, slot_samples, torch.int16 if pcm16 else torch.float32)
+        pool = PinnedSlotPool(n_slots, slot_samples, torch.int16 if pcm16 else torch.float32, label_floats=bs * int(dataset.label_num))
         args = dict(num_workers=num_workers, collate_fn=functools.partial(AudiosetDataset.collate, pool=pool), **kw)
         if num_workers > 0 and prefetch_factor is not None:
             args["prefetch_factor"] = prefetch_factor
@@ -475,6 +490,14 @@ class FrontendLoader:
         self._reap(block=True)
         if self.pool is not None:
             self.pool.close()
+
+    def host_labels(self, batch: RawBatch) -> torch.Tensor:
+        """The batch's [B, C] label matrix on the host: `batch.labels`, or -- for a pooled batch -- the view of its slot
+        (valid until the slot is released, i.e. until the batch's host -> device copy has finished)."""
+        if batch.labels is not None:
+            return batch.labels
+        n_lab = batch.labels_shape[0] * batch.labels_shape[1]
+        return self.pool.labels[batch.slot, :n_lab].view(batch.labels_shape)
 
     # ---- one batch ----
     def _reap(self, block: bool = False, keep: int = 0):
@@ -518,7 +541,7 @@ class FrontendLoader:
             self._dev_free[j] = None
         dst = self._dev[j][:nbytes].view(wav.dtype)
         labels_dev = None
-        lab = batch.labels
+        lab = self.host_labels(batch)
         if with_labels and not lab.is_pinned():  # small: stage through a page-locked ring so the copy stays asynchronous
             ring = self._label_ring[j]
             if ring is None or ring.numel() < lab.numel() or ring.dtype != lab.dtype:

@@ -71,12 +71,12 @@ with tempfile.TemporaryDirectory(dir="/dev/shm") as d:
         batch = next(it)
         t0 = time.perf_counter(); nn = int(batch.waves.offsets[-1] + (batch.waves.lengths[-1] + 3) // 4 * 4); wav = fl.pool.view(batch.slot, nn); tick("view", t0)
         t0 = time.perf_counter(); dst = devbuf[k % 3][:nn * 2].view(torch.int16); tick("dst", t0)
-        t0 = time.perf_counter(); ring[:batch.labels.numel()].copy_(batch.labels.reshape(-1)); tick("labels_ring", t0)
+        t0 = time.perf_counter(); hl = fl.host_labels(batch); ring[:hl.numel()].copy_(hl.reshape(-1)); tick("labels_ring", t0)
         t0 = time.perf_counter()
         with torch.cuda.stream(cs):
             dst.copy_(wav, non_blocking=True)
             tick("h2d_call", t0)
-            t0 = time.perf_counter(); lab = ring[:batch.labels.numel()].to(dev, non_blocking=True); tick("labels_h2d", t0)
+            t0 = time.perf_counter(); lab = ring[:hl.numel()].to(dev, non_blocking=True); tick("labels_h2d", t0)
             t0 = time.perf_counter(); ev = torch.cuda.Event(); ev.record(cs); tick("event", t0)
         t0 = time.perf_counter(); torch.cuda.current_stream(dev).wait_event(ev); tick("wait_event", t0)
         t0 = time.perf_counter(); fb = fe.forward_packed(PackedWaves(dst, batch.waves.offsets, batch.waves.lengths), batch.src1, batch.src2, batch.lam, batch.masks); tick("forward_packed", t0)

@@ -78,12 +78,15 @@ def test_pooled_collate_packs_into_shared_slots(files, golden_dir):
     import functools
     _, conf = _conf(golden_dir, "eval")
     ds = AudiosetDataset(files[0], conf, label_csv=files[1], loader=pcm16_loader, verbose=False)
-    pool = PinnedSlotPool(2, 2 * 4 * 40004, torch.int16, register=False)
+    g, _ = _conf(golden_dir, "eval")
+    pool = PinnedSlotPool(2, 2 * 4 * 40004, torch.int16, register=False, label_floats=4 * 10)
     dl = torch.utils.data.DataLoader(ds, batch_size=4, num_workers=2, collate_fn=functools.partial(AudiosetDataset.collate, pool=pool))
     waves = tiny_dataset_waves()
     seen = 0
     for batch in dl:
         assert batch.slot in (0, 1) and batch.waves.wav is None
+        assert batch.labels is None and batch.labels_shape == (len(batch), 10)  # the label matrix travels in the slot as well
+        assert np.array_equal(pool.labels[batch.slot, :len(batch) * 10].view(len(batch), 10).numpy(), g["eval_labels"][seen:seen + len(batch)])
         ref = pack_waveforms([to_pcm16(waves[(seen + b) % 8]) for b in range(len(batch))])
         n = ref.wav.numel()
         assert np.array_equal(batch.waves.offsets, ref.offsets) and torch.equal(pool.view(batch.slot, n), ref.wav)

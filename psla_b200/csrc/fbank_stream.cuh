@@ -97,7 +97,10 @@ PSLA_HDC int wpos(int u, int par) {
     return u < 240 ? par * kOvFloats + u : (u < 640 ? 2 * kOvFloats + 16 + (u - 240) + (u >= 320 ? 16 : 0) : (par ^ 1) * kOvFloats + (u - 640));
 }
 constexpr int kBsFloats = 56;  // 55 sums of 16 samples (one such array per parity: sums 40..54 are also the next group's 0..14)
-constexpr int kXsFloats = 8;   // (1-p) * x at u = 0, 160, 320, 480 (per parity; u = 640, 800 are the next group's 0, 160)
+constexpr int kXsFloats = 64;  // (1-p) * x at u = 0, 160, 320, 480 (per parity; u = 640, 800 are the next group's 0, 160), at xs_pos(u / 160)
+// Frames 0, 1 sit on bank 0 and frames 2, 3 on bank 16: the banks no other lane of the half-warp reads its staged sample
+// from in the same pass-1 load (lane 0 reads XS where lanes 1..15 read consecutive staged samples).
+PSLA_HDC int xs_pos(int f) { return (f & 1) * 32 + (f >> 1) * 16; }
 // Exchange buffer of one frame pair, organised by the ROW PAIRS pass 2 consumes: EX[t][n2] = (Z1[ka][n2], Z1[kb][n2]) with
 // ka = t, kb = 32 - t (t = 0: rows 0 and 16) -- 16 bytes per (t, n2), so pass 1 stores and pass 2 loads are all 128-bit.
 // Row stride 68 floats: the 8 lanes of a quarter-warp (4 consecutive t x 2 pairs) read 8 distinct 16-byte bank groups.
@@ -176,8 +179,8 @@ PSLA_HD void pair_pass1_load(int n2, int h, int par, const float* __restrict__ W
         const float* XS = WS + kWsXS + par * kXsFloats;
         // replicate-padded first samples: lane 0 reads (1-p)*x0 from XS instead of d[0]; an address select, so that
         // lane 0 does not get a code path of its own
-        const float* x0p = (n2 == 0) ? XS + 2 * h : pa;
-        const float* y0p = (n2 == 0) ? XS + 2 * h + 1 : pa + 160;
+        const float* x0p = (n2 == 0) ? XS + xs_pos(2 * h) : pa;
+        const float* y0p = (n2 == 0) ? XS + xs_pos(2 * h + 1) : pa + 160;
         float w[kWinRow];
         static_for<0, kWinRow / 4>([&](auto q_) {
             constexpr int q = decltype(q_)::value;

@@ -540,8 +540,8 @@ __device__ __forceinline__ void stage_commit(const MixState<S>& m, int S0, int l
             // u % 160 == 0  <=>  (U0/4 + L) % 40 == 0: at most one lane per iteration, known at compile time
             const int q = (U0 / 4 + 32 * it + 39) / 40;  // first multiple of 40 at or after this iteration's first float4
             if (U0 / 4 + L == 40 * q) {
-                if (q < 4) XSp[q] = c1 * x.x;
-                else XSo[q - 4] = c1 * x.x;
+                if (q < 4) XSp[xs_pos(q)] = c1 * x.x;
+                else XSo[xs_pos(q - 4)] = c1 * x.x;
             }
         }
     }

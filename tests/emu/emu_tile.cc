@@ -78,7 +78,7 @@ int emu_fbank_ordered(const float* x, int n, int num_bins, const float* mel_dens
             const float xc = s < n ? x[s] : 0.f;
             const float xp = (u > 0 && s - 1 < n) ? x[s - 1] : 0.f;
             W[wpos(u, par)] = fmaf(-p, xp, xc);
-            if (u % kFrameShift == 0 && u < kStepSamples) XS[u / kFrameShift] = c1 * xc;
+            if (u % kFrameShift == 0 && u < kStepSamples) XS[xs_pos(u / kFrameShift)] = c1 * xc;
         }
         for (int q = 0; q < kGroupSamples / 16; ++q) {
             // same association as the kernel: 4 x (sum of 4) combined by two xor-shuffle steps

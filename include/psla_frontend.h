@@ -36,7 +36,9 @@ typedef enum psla_status {
     PSLA_E_MASK = -4,         /* mask offsets outside [0, num_mel_bins] x [0, target_length] */
     PSLA_E_WORKSPACE = -5,    /* workspace too small / misaligned */
     PSLA_E_CUDA = -6,         /* a CUDA runtime call failed; psla_last_cuda_error() has the code */
-    PSLA_E_NOMEM = -7
+    PSLA_E_NOMEM = -7,
+    PSLA_E_STATIC_LIMIT = -8  /* psla_frontend_forward_static: more than PSLA_STATIC_MAX_CLIPS clips in one call, or the handle is in a
+                                 mode whose launches allocate (set_param_meta(0), set_timing(1)) */
 } psla_status;
 
 /* Replaces: the constants of the `kaldi.fbank(...)` call at audioset_dataset.py:119-120 plus the tables that
@@ -88,6 +90,33 @@ int psla_frontend_forward_host(psla_frontend_t* handle, const float* wav_host, i
                                int n_clips, int target_length, float norm_mean, float norm_div, int skip_norm,
                                float* out_host, void* stream);
 float* psla_frontend_device_out(const psla_frontend_t* handle);
+
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * psla_frontend_forward() with NO workspace argument and NO allocation: the device scratch of the call -- the per-clip partial
+ * sums `clip_stats_kernel` writes and `fbank_stream_kernel` reads (whole-clip means of exact_clip_mean mode and of mixup partners
+ * shorter than their clip) -- lives in a file-scope `static __device__` array of the library, sized for at most
+ * PSLA_STATIC_MAX_CLIPS clips per call (PSLA_STATIC_SCRATCH_BYTES, held by every GPU that loads the library until the process
+ * exits).  Inputs and outputs are the caller's, with the meaning and checks of psla_frontend_forward(); results are bit-identical
+ * to it.  The call makes no cudaMalloc / cudaFree / cudaHostAlloc and calls no allocating library routine: descriptors travel in
+ * the kernels' parameter space, the array's device address was resolved (cudaGetSymbolAddress) when the handle was created.
+ *
+ *   n_clips > PSLA_STATIC_MAX_CLIPS                           -> PSLA_E_STATIC_LIMIT (split the batch, or use forward())
+ *   handle with set_param_meta(0) or set_timing(1)            -> PSLA_E_STATIC_LIMIT (those modes allocate per launch)
+ *   the symbol's address could not be resolved at create()    -> PSLA_E_CUDA (psla_last_cuda_error() has the code)
+ *
+ * ONE array per GPU, shared by every handle and every call: it keeps the last call's contents (nothing in it has to start at
+ * zero -- every partial sum a call reads is written by that call's own statistics kernel first), and calls that OVERLAP ON THE
+ * GPU RACE on it.  Calls through one handle on one stream are safe (consecutive calls rotate through three partial-sum
+ * regions exactly like forward() rotates through its workspace); calls from two handles, or on two streams, that need the
+ * statistics pass must be ordered by the caller.  Batches without a statistics pass never touch the array. */
+#define PSLA_STATIC_MAX_CLIPS 128
+#define PSLA_STATIC_SCRATCH_BYTES (512 * 1024)
+int psla_frontend_forward_static(psla_frontend_t* handle, const float* wav, int64_t wav_samples, const int64_t* wav_offset,
+                                 const int64_t* wav_length, int n_wav, const int32_t* src1, const int32_t* src2,
+                                 const double* lambda, const int32_t* mask, int n_clips, int target_length, float norm_mean,
+                                 float norm_div, int skip_norm, float* out, void* stream);
 
 /* The same two calls for 16-bit PCM waveforms as they come out of a wav file (the reference decodes them with
  * torchaudio.load, audioset_dataset.py:91,95-96, whose normalisation is value / 32768; the kernel applies exactly that

@@ -13,7 +13,7 @@ from .build import LIB
 
 PSLA_OK = 0
 STATUS_NAMES = {0: "PSLA_OK", -1: "PSLA_E_INVALID", -2: "PSLA_E_UNSUPPORTED", -3: "PSLA_E_SHORT_CLIP",
-                -4: "PSLA_E_MASK", -5: "PSLA_E_WORKSPACE", -6: "PSLA_E_CUDA", -7: "PSLA_E_NOMEM"}
+                -4: "PSLA_E_MASK", -5: "PSLA_E_WORKSPACE", -6: "PSLA_E_CUDA", -7: "PSLA_E_NOMEM", -8: "PSLA_E_STATIC_LIMIT"}
 
 # every symbol include/psla_frontend.h declares: name -> (restype, argtypes).  The host metadata arrays of the forward entry
 # points (int64 / int32 / double pointers in the header) are bound as void*: the caller passes the numpy buffers' addresses as
@@ -32,6 +32,8 @@ SYMBOLS = {
                                            c_void_p, c_void_p, c_int, c_int, c_float, c_float, c_int,
                                            c_void_p, c_void_p]),
     "psla_frontend_device_out": (c_void_p, [c_void_p]),
+    "psla_frontend_forward_static": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
+                                             c_void_p, c_void_p, c_int, c_int, c_float, c_float, c_int, c_void_p, c_void_p]),
     "psla_frontend_forward_pcm16": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int, c_void_p, c_void_p,
                                             c_void_p, c_void_p, c_int, c_int, c_float, c_float, c_int,
                                             c_void_p, c_void_p, c_size_t, c_void_p]),

@@ -22,6 +22,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -39,6 +40,21 @@ constexpr int kMetaSlots = 4;
 constexpr int kPartialSlots = 3;  // partial-sum buffers of the statistics kernel, rotated: the statistics pass of call k + 1 may run while the streaming kernel of call k still reads its own
 constexpr int kCtasPerSm = 4;  // __launch_bounds__(kThreads, 4): 4 warps x 128 registers and ~53 KB of shared memory per CTA
 constexpr size_t kSmemPerSm = 228 * 1024, kSmemPerCtaReserved = 1024, kSmemPerCtaMax = 227 * 1024;
+
+// ---- scratch of the allocation-free entry point (psla_frontend_forward_static; no counterpart in the reference) ----
+// A file-scope device array: every GPU that loads this library holds PSLA_STATIC_SCRATCH_BYTES of it until the process
+// exits.  Laid out like a forward() workspace for PSLA_STATIC_MAX_CLIPS clips (descriptor slots, unused on this path, then
+// the kPartialSlots partial-sum regions of clip_stats_kernel).  In HOST code `g_static_scratch` is only a stand-in for
+// the symbol, not a device address: static_scratch_address() resolves it once per device with cudaGetSymbolAddress and
+// only that pointer is ever passed to a kernel.
+constexpr size_t kStaticScratchBytes = PSLA_STATIC_SCRATCH_BYTES;
+constexpr size_t static_align(size_t v, size_t a) { return (v + a - 1) / a * a; }
+constexpr size_t kStaticScratchNeed =
+    kMetaSlots * (static_align(size_t(PSLA_STATIC_MAX_CLIPS) * sizeof(ClipDesc), 256) + static_align((size_t(PSLA_STATIC_MAX_CLIPS) + 1) * sizeof(ClipCost), 256)) +
+    kPartialSlots * static_align(size_t(PSLA_STATIC_MAX_CLIPS) * kStatSegs * kStatVals * sizeof(double), 256);
+static_assert(kStaticScratchNeed <= kStaticScratchBytes, "PSLA_STATIC_SCRATCH_BYTES does not hold PSLA_STATIC_MAX_CLIPS clips");
+static_assert(PSLA_STATIC_MAX_CLIPS <= kParamClips, "the allocation-free path passes descriptors as kernel parameters");
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
 
 struct psla_frontend {
     int device = 0;
@@ -103,6 +119,9 @@ struct psla_frontend {
     size_t d_out_cap = 0;
     void* d_ws = nullptr;
     size_t d_ws_cap = 0;
+    // device address of g_static_scratch on `device` (resolved in create(); forward_static only)
+    void* static_scratch = nullptr;
+    int static_scratch_err = 0;
 };
 
 namespace {
@@ -129,6 +148,30 @@ struct DeviceGuard {
     } while (0)
 
 size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// Device address of g_static_scratch on the CURRENT device; resolved once per device (the symbol has one instance per
+// device, and cudaGetSymbolAddress answers for the device that is current).  Returns the CUDA error code of the query.
+int static_scratch_address(int device, void** ptr) {
+    constexpr int kMaxDevices = 64;
+    static std::mutex mu;
+    static void* cached[kMaxDevices] = {};
+    *ptr = nullptr;
+    std::lock_guard<std::mutex> lock(mu);
+    if (device >= 0 && device < kMaxDevices && cached[device]) {
+        *ptr = cached[device];
+        return 0;
+    }
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return static_cast<int>(e);
+    }
+    if (!p || (reinterpret_cast<uintptr_t>(p) & 255)) return static_cast<int>(cudaErrorInvalidSymbol);
+    if (device >= 0 && device < kMaxDevices) cached[device] = p;
+    *ptr = p;
+    return 0;
+}
 
 __global__ void probe_lg2_kernel(float x, float* out) { *out = lg2_ftz(x); }
 int probe_lg2_eps(psla_frontend* h) {
@@ -284,6 +327,9 @@ const char* psla_strerror(int s) {
         case PSLA_E_WORKSPACE: return "workspace too small or misaligned";
         case PSLA_E_CUDA: return "CUDA runtime error";
         case PSLA_E_NOMEM: return "out of memory";
+        case PSLA_E_STATIC_LIMIT:
+            return "forward_static: more than PSLA_STATIC_MAX_CLIPS (128) clips in one call, or a handle mode that allocates per launch "
+                   "(set_param_meta(0) / set_timing(1)); split the batch or use psla_frontend_forward with a workspace";
         default: return "unknown status";
     }
 }
@@ -324,6 +370,7 @@ int psla_frontend_create(psla_frontend_t** handle, int device, int sample_rate, 
     }
     int st = upload_tables(h);
     if (st == PSLA_OK) st = probe_lg2_eps(h);
+    h->static_scratch_err = static_scratch_address(device, &h->static_scratch);  // reported by forward_static, nobody else needs it
     if (st == PSLA_OK) {
         for (auto& s : h->slots)
             if (cudaEventCreateWithFlags(&s.copied, cudaEventDisableTiming) != cudaSuccess ||
@@ -918,6 +965,24 @@ int psla_frontend_forward_pcm16(psla_frontend_t* h, const int16_t* wav, int64_t 
                                 size_t workspace_bytes, void* stream) {
     return forward_any(h, wav, wav_samples, true, wav_offset, wav_length, n_wav, src1, src2, lambda, mask, n_clips, target_length, norm_mean, norm_div,
                        skip_norm, out, workspace, workspace_bytes, stream);
+}
+
+// No counterpart in the reference (see the header).  forward() over the library's static device scratch: with at most
+// kParamClips clips and descriptors in parameter space, forward_any / enqueue_batch touch neither the host vectors nor a
+// pinned slot, so the call consists of the validation loop and one or two cudaLaunchKernelEx.
+int psla_frontend_forward_static(psla_frontend_t* h, const float* wav, int64_t wav_samples, const int64_t* wav_offset, const int64_t* wav_length,
+                                 int n_wav, const int32_t* src1, const int32_t* src2, const double* lambda, const int32_t* mask, int n_clips,
+                                 int target_length, float norm_mean, float norm_div, int skip_norm, float* out, void* stream) {
+    if (!h) return PSLA_E_INVALID;
+    if (n_clips > PSLA_STATIC_MAX_CLIPS) return PSLA_E_STATIC_LIMIT;
+    if (!h->param_meta || h->timing) return PSLA_E_STATIC_LIMIT;  // a pinned descriptor slot / timing events would be created
+    if (h->static_scratch_err != 0 || !h->static_scratch) {
+        h->last_cuda = h->static_scratch_err ? h->static_scratch_err : static_cast<int>(cudaErrorInvalidSymbol);
+        return PSLA_E_CUDA;
+    }
+    if (n_clips > 0 && psla_frontend_workspace_bytes(h, n_clips) > kStaticScratchBytes) return PSLA_E_STATIC_LIMIT;
+    return forward_any(h, wav, wav_samples, false, wav_offset, wav_length, n_wav, src1, src2, lambda, mask, n_clips, target_length, norm_mean, norm_div,
+                       skip_norm, out, h->static_scratch, kStaticScratchBytes, stream);
 }
 
 float* psla_frontend_device_out(const psla_frontend_t* h) { return h ? h->d_out : nullptr; }

@@ -30,7 +30,8 @@ typedef struct psla_frontend psla_frontend_t;
 typedef enum psla_status {
     PSLA_OK = 0,
     PSLA_E_INVALID = -1,      /* null pointer, negative size, index out of range, misaligned buffer */
-    PSLA_E_UNSUPPORTED = -2,  /* geometry other than 400/160/512 (16 kHz, 25 ms / 10 ms) or > 128 mel bins */
+    PSLA_E_UNSUPPORTED = -2,  /* a frame whose FFT size falls outside [64, 4096] points, > 128 mel bins, or an option that exists
+                                 for the 16 kHz streaming kernel only (output layouts, timeline) on the generic path */
     PSLA_E_SHORT_CLIP = -3,   /* a primary waveform has fewer samples than one frame; the reference raises
                                  AssertionError at torchaudio/compliance/kaldi.py:142 */
     PSLA_E_MASK = -4,         /* mask offsets outside [0, num_mel_bins] x [0, target_length] */
@@ -43,14 +44,19 @@ typedef enum psla_status {
 
 /* Replaces: the constants of the `kaldi.fbank(...)` call at audioset_dataset.py:119-120 plus the tables that
  * call rebuilds every time (torchaudio/compliance/kaldi.py:94-95 Hann window, :436-511 get_mel_banks).
- * high_freq <= 0 means "offset from Nyquist" exactly like kaldi.py:457-458. */
+ * high_freq <= 0 means "offset from Nyquist" exactly like kaldi.py:457-458.
+ * Geometry (kaldi.py:138-140): frame length int(sample_rate * frame_length_ms / 1000), shift int(sample_rate *
+ * frame_shift_ms / 1000), FFT size the next power of two.  400 / 160 / 512 (16 kHz, 25 / 10 ms: every recipe of the reference)
+ * runs the fused streaming kernel; any other geometry with an FFT of 64..4096 points (8 kHz ... 48 kHz and beyond at 25 / 10 ms)
+ * runs a geometry-generic kernel: same results contract, clip means always from the statistics kernel, [B, T, F] fp32 output
+ * only, not tuned for the roofline. */
 int psla_frontend_create(psla_frontend_t** handle, int device, int sample_rate, int num_mel_bins,
                          float frame_length_ms, float frame_shift_ms, float preemph, float low_freq,
                          float high_freq);
 void psla_frontend_destroy(psla_frontend_t* handle);
 
 /* Optional: replace the natively built tables (host pointers).  `window` is [frame_length] = the analysis
- * window itself (NOT pre-halved); `mel` is the dense [num_mel_bins][nfft/2] weight matrix.  Either may be
+ * window itself (NOT pre-halved); `mel` is the dense [num_mel_bins][nfft/2] weight matrix (psla_frontend_get_geometry).  Either may be
  * NULL.  The Python host uses this to install tables built with torch ops in torchaudio's op order. */
 int psla_frontend_set_tables(psla_frontend_t* handle, const float* window, const float* mel);
 /* Read the tables back (host pointers, same shapes; either may be NULL). */
@@ -103,7 +109,8 @@ float* psla_frontend_device_out(const psla_frontend_t* handle);
  * the kernels' parameter space, the array's device address was resolved (cudaGetSymbolAddress) when the handle was created.
  *
  *   n_clips > PSLA_STATIC_MAX_CLIPS                           -> PSLA_E_STATIC_LIMIT (split the batch, or use forward())
- *   handle with set_param_meta(0) or set_timing(1)            -> PSLA_E_STATIC_LIMIT (those modes allocate per launch)
+ *   handle with set_param_meta(0), set_timing(1) or on the
+ *   geometry-generic path (not 16 kHz / set_generic_path)    -> PSLA_E_STATIC_LIMIT (those modes allocate per launch)
  *   the symbol's address could not be resolved at create()    -> PSLA_E_CUDA (psla_last_cuda_error() has the code)
  *
  * ONE array per GPU, shared by every handle and every call: it keeps the last call's contents (nothing in it has to start at
@@ -144,6 +151,12 @@ int psla_frontend_noise_roll(psla_frontend_t* handle, const float* in, float* ou
 
 /* Number of frames kaldi.fbank produces for n_samples (snip_edges=True, kaldi.py:63-67); < 0 if too short. */
 int psla_frontend_num_frames(const psla_frontend_t* handle, int64_t n_samples);
+/* Frame length, frame shift and FFT size of the handle in samples (kaldi.py:138-140), and whether forward() runs the
+ * geometry-generic kernel (any pointer may be NULL). */
+int psla_frontend_get_geometry(const psla_frontend_t* handle, int* frame_length, int* frame_shift, int* fft_size, int* generic_path);
+/* 1: run the 16 kHz geometry through the geometry-generic kernel as well (an independent second implementation of the
+ * recipe: the tests compare the streaming kernel with it); 0 (default): the streaming kernel.  No effect on other geometries. */
+int psla_frontend_set_generic_path(psla_frontend_t* handle, int enable);
 /* Kernels launched by this handle since creation (bench.py reports it as gpu_launches). */
 int64_t psla_frontend_launch_count(const psla_frontend_t* handle);
 /* Select the log implementation: 0 = logf (default), 1 = lg2.approx based (abs err < 4e-6 on log-mel). */

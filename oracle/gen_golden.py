@@ -10,6 +10,7 @@ What is pinned (the reference has no tests of its own):
   * tables.npz        -- ``kaldi.get_mel_banks`` nnz + ``torch.hann_window`` as used by the call
   * mask_offsets.npz  -- cells masked by the real Frequency/TimeMasking modules for 200 seeds
   * getitem_*.npz     -- full ``AudiosetDataset.__getitem__`` outputs on a tiny in-memory dataset
+  * getitem_rates.npz -- ``__getitem__`` with ``torchaudio.load`` reporting 8 / 22.05 / 32 / 44.1 / 48 kHz (other frame geometries)
   * getitem_files.npz -- the same class reading REAL 16-bit wav files (written by psla_b200.synth.write_tiny_wav_dataset;
                          ``torchaudio.load`` replaced by a wav reader with its int16 normalisation, value / 32768)
 """
@@ -141,6 +142,37 @@ def gen_getitem(AudiosetDataset, only=None):
             print("getitem", name, np.stack(feats).shape)
 
 
+RATES = (8000, 22050, 32000, 44100, 48000)
+
+
+def gen_getitem_rates(AudiosetDataset):
+    """The unmodified reference class on waveforms at OTHER sample rates: `torchaudio.load` hands (wave, sr) back and the
+    reference passes `sample_frequency=sr` on to kaldi.fbank (audioset_dataset.py:91,119), which derives the frame
+    geometry from it (kaldi.py:138-140: 200/80/256 at 8 kHz ... 1200/480/2048 at 48 kHz).  Train conf, seeded."""
+    waves = tiny_dataset_waves()
+    conf = {"num_mel_bins": 128, "target_length": 48, "freqm": 24, "timem": 12, "mixup": 0.5,
+            "dataset": "audioset", "mode": "train", "mean": -4.6476, "std": 4.5699, "noise": False}
+    out = {}
+    with tempfile.TemporaryDirectory() as tmp:
+        jpath, cpath = write_tiny_dataset(tmp, waves)
+        store = {f"mem://{i}.wav": w for i, w in enumerate(waves)}
+        for sr in RATES:
+            torchaudio.load = lambda path, sr=sr: (store[path].clone(), sr)
+            ds = AudiosetDataset(jpath, audio_conf=conf, label_csv=cpath)
+            feats, labels = [], []
+            random.seed(sr)
+            np.random.seed(sr)
+            torch.manual_seed(sr)
+            for i in range(len(ds)):
+                fb, lab = ds[i]
+                feats.append(fb.numpy())
+                labels.append(lab.numpy())
+            out[f"feats_{sr}"] = np.stack(feats)
+            out[f"labels_{sr}"] = np.stack(labels)
+            print("getitem_rates", sr, out[f"feats_{sr}"].shape)
+    np.savez_compressed(os.path.join(GOLD, "getitem_rates.npz"), conf=json.dumps(conf), rates=np.array(RATES), **out)
+
+
 def gen_getitem_files(AudiosetDataset):
     """The unmodified reference class over real wav files: eval conf (deterministic) and train conf (seeded, single process)."""
     import wave
@@ -185,7 +217,9 @@ def main():
     if len(sys.argv) > 1:  # e.g. `python oracle/gen_golden.py noise`: (re)generate only the named __getitem__ fixtures
         if "files" in sys.argv[1:]:
             gen_getitem_files(import_reference_dataset())
-        rest = set(sys.argv[1:]) - {"files"}
+        if "rates" in sys.argv[1:]:
+            gen_getitem_rates(import_reference_dataset())
+        rest = set(sys.argv[1:]) - {"files", "rates"}
         if rest:
             gen_getitem(import_reference_dataset(), only=rest)
         return
@@ -194,6 +228,7 @@ def main():
     gen_mask_offsets()
     gen_getitem(import_reference_dataset())
     gen_getitem_files(import_reference_dataset())
+    gen_getitem_rates(import_reference_dataset())
     meta = {"torch": torch.__version__, "torchaudio": torchaudio.__version__, "numpy": np.__version__,
             "reference": "/root/reference (haoheliu/psla), src/dataloaders/audioset_dataset.py unmodified",
             "pinned_in_reference_requirements": "torchaudio==0.6.0 torch==1.6.0 (not installable here)"}

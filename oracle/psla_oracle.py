@@ -302,7 +302,7 @@ class ItemDraw:
 
 
 def item_torch(waves: Sequence[torch.Tensor], index: int, audio_conf: dict, py_random, np_random=np.random,
-               use_torchaudio: bool = True) -> Tuple[torch.Tensor, ItemDraw]:
+               use_torchaudio: bool = True, sample_rate: float = SAMPLE_RATE) -> Tuple[torch.Tensor, ItemDraw]:
     """Restatement of ``AudiosetDataset.__getitem__`` (features only, labels live in
     ``psla_b200.dataloaders`` host code) for in-memory waveforms ``waves[i]`` ([1, n_i]).
 
@@ -315,11 +315,11 @@ def item_torch(waves: Sequence[torch.Tensor], index: int, audio_conf: dict, py_r
     if py_random.random() < mixup:
         partner = py_random.randint(0, len(waves) - 1)
         lam = float(np_random.beta(10, 10))
-        fb = wav2fbank_torch(waves[index], waves[partner], lam, T, F, use_torchaudio=use_torchaudio)
+        fb = wav2fbank_torch(waves[index], waves[partner], lam, T, F, sample_rate=sample_rate, use_torchaudio=use_torchaudio)
         mixed = True
     else:
         partner, lam, mixed = -1, 0.0, False
-        fb = wav2fbank_torch(waves[index], None, 0.0, T, F, use_torchaudio=use_torchaudio)
+        fb = wav2fbank_torch(waves[index], None, 0.0, T, F, sample_rate=sample_rate, use_torchaudio=use_torchaudio)
     mask = draw_mask_offsets(audio_conf.get("freqm"), audio_conf.get("timem"), F, T)
     skip = bool(audio_conf.get("skip_norm")) if audio_conf.get("skip_norm") else False
     out = apply_masks_and_norm_torch(fb, mask, audio_conf.get("mean"), audio_conf.get("std"), skip)
@@ -337,7 +337,7 @@ def noise_roll_torch(fbank: torch.Tensor, field: torch.Tensor, scale: float, shi
 def batch_torch(waves: Sequence[torch.Tensor], src1: Sequence[int], src2: Sequence[int], lam: Sequence[float],
                 masks: Sequence[Sequence[int]], target_length: int, norm_mean: float, norm_div: float,
                 skip_norm: bool = False, num_mel_bins: int = 128, use_torchaudio: bool = True,
-                dtype=torch.float32) -> torch.Tensor:
+                dtype=torch.float32, sample_rate: float = SAMPLE_RATE) -> torch.Tensor:
     """Batch oracle with explicit parameters (the same arguments the C-ABI takes):
     out[b] = norm(mask(pad(fbank(mix(waves[src1[b]], waves[src2[b]], lam[b])))))."""
     outs = []
@@ -345,10 +345,10 @@ def batch_torch(waves: Sequence[torch.Tensor], src1: Sequence[int], src2: Sequen
         w1 = waves[src1[b]].to(dtype)
         w2 = waves[src2[b]].to(dtype) if src2[b] >= 0 else None
         if dtype == torch.float32:
-            fb = wav2fbank_torch(w1, w2, float(lam[b]), target_length, num_mel_bins, use_torchaudio=use_torchaudio)
+            fb = wav2fbank_torch(w1, w2, float(lam[b]), target_length, num_mel_bins, sample_rate=sample_rate, use_torchaudio=use_torchaudio)
         else:
             wave = mix_waveforms_torch(w1, w2, float(lam[b]))
-            fb = pad_or_truncate(ref_fbank(wave, num_mel_bins) if use_torchaudio else
-                                 kaldi_fbank_torch(wave[0], num_mel_bins), target_length)
+            fb = pad_or_truncate(ref_fbank(wave, num_mel_bins, sample_rate) if use_torchaudio else
+                                 kaldi_fbank_torch(wave[0], num_mel_bins, sample_rate), target_length)
         outs.append(apply_masks_and_norm_torch(fb, masks[b], norm_mean, norm_div, skip_norm))
     return torch.stack(outs)

@@ -44,6 +44,8 @@ SYMBOLS = {
                                          ctypes.c_uint64, c_void_p]),
     "psla_frontend_num_frames": (c_int, [c_void_p, c_int64]),
     "psla_frontend_launch_count": (c_int64, [c_void_p]),
+    "psla_frontend_get_geometry": (c_int, [c_void_p, POINTER(c_int), POINTER(c_int), POINTER(c_int), POINTER(c_int)]),
+    "psla_frontend_set_generic_path": (c_int, [c_void_p, c_int]),
     "psla_frontend_set_fast_log": (c_int, [c_void_p, c_int]),
     "psla_frontend_set_exact_clip_mean": (c_int, [c_void_p, c_int]),
     "psla_frontend_set_output_layout": (c_int, [c_void_p, c_int]),

@@ -29,6 +29,7 @@
 #include "../../include/psla_frontend.h"
 #include "noise_roll.cuh"
 #include "stream_kernel.cuh"
+#include "generic_kernel.cuh"
 #include "tables.h"
 
 // ================================================================================================
@@ -62,8 +63,16 @@ struct psla_frontend {
     int nmel = 128;
     float preemph = 0.97f;
     float low_freq = 20.f, high_freq = 0.f;
-    std::vector<float> window;     // [400] analysis window (not halved)
-    std::vector<float> mel_dense;  // [nmel][256]
+    // frame geometry, kaldi.py:138-140: int(sr * 25 ms), int(sr * 10 ms), next power of two.  400 / 160 / 512 (16 kHz) runs
+    // the streaming kernel; every other geometry (or generic_forced) the geometry-generic kernel of generic_kernel.cuh.
+    int frame_len = kFrameLen, frame_shift = kFrameShift, nfft = kNfft;
+    bool native_geometry = true;  // 400 / 160 / 512
+    bool generic_forced = false;  // psla_frontend_set_generic_path
+    bool generic() const { return !native_geometry || generic_forced; }
+    float* d_gen = nullptr;       // tables of the generic kernel: window | tw | twn | mel_range | mel_w
+    size_t gen_off_tw = 0, gen_off_twn = 0, gen_off_range = 0, gen_off_w = 0;
+    std::vector<float> window;     // [frame_len] analysis window (not halved)
+    std::vector<float> mel_dense;  // [nmel][nfft / 2]
     float* d_tab = nullptr;
     int tab_floats = 0;
     size_t smem_bytes = 0;
@@ -283,7 +292,60 @@ cudaError_t prepare_all(size_t smem) {
 }
 #endif
 
+// Tables of the geometry-generic kernel (generic_kernel.cuh), built for every handle (a few hundred KB at most): the 16 kHz
+// geometry can be switched onto that kernel as well (psla_frontend_set_generic_path).
+int upload_generic_tables(psla_frontend* h) {
+    const int L = h->frame_len, N = h->nfft, M = N / 2, nmel = h->nmel;
+    const size_t off_tw = align_up(static_cast<size_t>(L), 4);
+    const size_t off_twn = off_tw + static_cast<size_t>(M);             // M/2 complex
+    const size_t off_range = off_twn + align_up(static_cast<size_t>(M) + 2, 4);  // M/2 + 1 complex
+    const size_t off_w = off_range + align_up(2 * static_cast<size_t>(nmel), 4);
+    const size_t total = off_w + static_cast<size_t>(nmel) * M;
+    std::vector<float> buf(total, 0.f);
+    std::memcpy(buf.data(), h->window.data(), sizeof(float) * L);
+    const double two_pi = 6.283185307179586476925286766559;
+    for (int j = 0; j < M / 2; ++j) {
+        buf[off_tw + 2 * j] = static_cast<float>(std::cos(two_pi * j / M));
+        buf[off_tw + 2 * j + 1] = static_cast<float>(-std::sin(two_pi * j / M));
+    }
+    for (int k = 0; k <= M / 2; ++k) {
+        buf[off_twn + 2 * k] = static_cast<float>(std::cos(two_pi * k / N));
+        buf[off_twn + 2 * k + 1] = static_cast<float>(-std::sin(two_pi * k / N));
+    }
+    int* range = reinterpret_cast<int*>(buf.data() + off_range);
+    for (int m = 0; m < nmel; ++m) {
+        const float* row = h->mel_dense.data() + static_cast<size_t>(m) * M;
+        int lo = 0, hi = 0;
+        for (int k = 0; k < M; ++k)
+            if (row[k] != 0.f) {
+                if (hi == 0) lo = k;
+                hi = k + 1;
+            }
+        range[2 * m] = lo;
+        range[2 * m + 1] = hi;
+    }
+    std::memcpy(buf.data() + off_w, h->mel_dense.data(), sizeof(float) * static_cast<size_t>(nmel) * M);
+    if (h->d_gen) {
+        PSLA_CUDA(h, cudaDeviceSynchronize());
+        cudaFree(h->d_gen);
+        h->d_gen = nullptr;
+    }
+    PSLA_CUDA(h, cudaMalloc(&h->d_gen, total * sizeof(float)));
+    PSLA_CUDA(h, cudaMemcpy(h->d_gen, buf.data(), total * sizeof(float), cudaMemcpyHostToDevice));
+    h->gen_off_tw = off_tw;
+    h->gen_off_twn = off_twn;
+    h->gen_off_range = off_range;
+    h->gen_off_w = off_w;
+    const int smem = static_cast<int>(generic_smem_bytes(N));
+    PSLA_CUDA(h, cudaFuncSetAttribute(fbank_generic_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    PSLA_CUDA(h, cudaFuncSetAttribute(fbank_generic_kernel<short>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    PSLA_CUDA(h, cudaDeviceGetAttribute(&h->num_sms, cudaDevAttrMultiProcessorCount, h->device));
+    return PSLA_OK;
+}
+
 int upload_tables(psla_frontend* h) {
+    const int gst = upload_generic_tables(h);
+    if (gst != PSLA_OK || !h->native_geometry) return gst;
     std::vector<float> buf;
     bool spec = false;
     if (!build_table_buffer(h->window.data(), h->mel_dense.data(), h->nmel, &buf, &spec)) return PSLA_E_UNSUPPORTED;
@@ -309,7 +371,10 @@ int upload_tables(psla_frontend* h) {
     return PSLA_OK;
 }
 
-int64_t frames_of(int64_t n) { return n < kFrameLen ? -1 : 1 + (n - kFrameLen) / kFrameShift; }
+int64_t frames_of(const psla_frontend* h, int64_t n) {  // _get_strided, kaldi.py:63-67 (snip_edges)
+    const int len = h ? h->frame_len : kFrameLen, shift = h ? h->frame_shift : kFrameShift;
+    return n < len ? -1 : 1 + (n - len) / shift;
+}
 
 }  // namespace
 
@@ -343,7 +408,9 @@ int psla_frontend_create(psla_frontend_t** handle, int device, int sample_rate, 
     // int(sample_frequency * frame_shift * 0.001), kaldi.py:138-139
     const int shift = static_cast<int>(static_cast<double>(sample_rate) * static_cast<double>(frame_shift_ms) * 0.001);
     const int size = static_cast<int>(static_cast<double>(sample_rate) * static_cast<double>(frame_length_ms) * 0.001);
-    if (shift != kFrameShift || size != kFrameLen) return PSLA_E_UNSUPPORTED;
+    int nfft = 1;
+    while (nfft < size) nfft <<= 1;  // round_to_power_of_two, kaldi.py:140
+    if (shift < 1 || size < 2 || nfft < kGenMinFft || nfft > kGenMaxFft) return PSLA_E_UNSUPPORTED;
     if (num_mel_bins < 4 || num_mel_bins > kMaxMel) return PSLA_E_UNSUPPORTED;  // kaldi.py:452 needs > 3
     if (!(preemph >= 0.f && preemph <= 1.f)) return PSLA_E_INVALID;              // kaldi.py:149
     const float nyq = 0.5f * sample_rate;
@@ -357,12 +424,16 @@ int psla_frontend_create(psla_frontend_t** handle, int device, int sample_rate, 
     h->preemph = preemph;
     h->low_freq = low_freq;
     h->high_freq = high_freq;
-    h->window.resize(kFrameLen);
-    std::vector<float> half(kFrameLen);
-    build_window_half(half.data(), kFrameLen);
-    for (int j = 0; j < kFrameLen; ++j) h->window[j] = 2.f * half[j];
-    h->mel_dense.resize(static_cast<size_t>(num_mel_bins) * (kNfft / 2));
-    build_mel_dense(h->mel_dense.data(), num_mel_bins, kNfft, static_cast<float>(sample_rate), low_freq, high_freq);
+    h->frame_len = size;
+    h->frame_shift = shift;
+    h->nfft = nfft;
+    h->native_geometry = (size == kFrameLen && shift == kFrameShift && nfft == kNfft);
+    h->window.resize(size);
+    std::vector<float> half(size);
+    build_window_half(half.data(), size);
+    for (int j = 0; j < size; ++j) h->window[j] = 2.f * half[j];
+    h->mel_dense.resize(static_cast<size_t>(num_mel_bins) * (nfft / 2));
+    build_mel_dense(h->mel_dense.data(), num_mel_bins, nfft, static_cast<float>(sample_rate), low_freq, high_freq);
     DeviceGuard guard(device);
     if (!guard.ok) {
         delete h;
@@ -399,6 +470,7 @@ void psla_frontend_destroy(psla_frontend_t* h) {
     }
     if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     if (h->d_tab) cudaFree(h->d_tab);
+    if (h->d_gen) cudaFree(h->d_gen);
     if (h->d_wav) cudaFree(h->d_wav);
     if (h->d_out) cudaFree(h->d_out);
     if (h->d_ws) cudaFree(h->d_ws);
@@ -408,7 +480,7 @@ void psla_frontend_destroy(psla_frontend_t* h) {
 int psla_frontend_set_tables(psla_frontend_t* h, const float* window, const float* mel) {
     if (!h) return PSLA_E_INVALID;
     std::vector<float> w0 = h->window, m0 = h->mel_dense;
-    if (window) std::memcpy(h->window.data(), window, sizeof(float) * kFrameLen);
+    if (window) std::memcpy(h->window.data(), window, sizeof(float) * h->window.size());
     if (mel) std::memcpy(h->mel_dense.data(), mel, sizeof(float) * h->mel_dense.size());
     DeviceGuard guard(h->device);
     if (!guard.ok) return PSLA_E_CUDA;
@@ -423,7 +495,7 @@ int psla_frontend_set_tables(psla_frontend_t* h, const float* window, const floa
 
 int psla_frontend_get_tables(const psla_frontend_t* h, float* window, float* mel) {
     if (!h) return PSLA_E_INVALID;
-    if (window) std::memcpy(window, h->window.data(), sizeof(float) * kFrameLen);
+    if (window) std::memcpy(window, h->window.data(), sizeof(float) * h->window.size());
     if (mel) std::memcpy(mel, h->mel_dense.data(), sizeof(float) * h->mel_dense.size());
     return PSLA_OK;
 }
@@ -470,8 +542,7 @@ int psla_frontend_noise_roll(psla_frontend_t* h, const float* in, float* out, co
 }
 
 int psla_frontend_num_frames(const psla_frontend_t* h, int64_t n_samples) {
-    (void)h;
-    const int64_t m = frames_of(n_samples);
+    const int64_t m = frames_of(h, n_samples);
     return m > 0x7fffffff ? 0x7fffffff : static_cast<int>(m);
 }
 
@@ -530,6 +601,21 @@ int psla_frontend_set_launch_overlap(psla_frontend_t* h, int mode) {
     return PSLA_OK;
 }
 
+int psla_frontend_set_generic_path(psla_frontend_t* h, int enable) {
+    if (!h) return PSLA_E_INVALID;
+    h->generic_forced = enable != 0;
+    return PSLA_OK;
+}
+
+int psla_frontend_get_geometry(const psla_frontend_t* h, int* frame_length, int* frame_shift, int* fft_size, int* generic_path) {
+    if (!h) return PSLA_E_INVALID;
+    if (frame_length) *frame_length = h->frame_len;
+    if (frame_shift) *frame_shift = h->frame_shift;
+    if (fft_size) *fft_size = h->nfft;
+    if (generic_path) *generic_path = h->generic() ? 1 : 0;
+    return PSLA_OK;
+}
+
 int psla_frontend_set_param_meta(psla_frontend_t* h, int enable) {
     if (!h) return PSLA_E_INVALID;
     h->param_meta = enable ? 1 : 0;
@@ -583,7 +669,8 @@ int enqueue_batch(psla_frontend_t* h, const void* wav, bool pcm16, ClipDesc* des
     // Small batches read their descriptors from the kernels' parameter space (the statistics kernel's too): nothing is
     // uploaded and, without a statistics pass, nothing sits between two launches on the stream.  Otherwise: pinned slot
     // -> device slot of the workspace on the copy stream, the kernels ordered after it by an event.
-    const bool param_meta = small && h->param_meta;
+    const bool generic = h->generic();
+    const bool param_meta = small && h->param_meta && !generic;  // the generic kernel reads its descriptors from device memory
     ClipDesc* d_desc = nullptr;
     ClipCost* d_cost = nullptr;
     const size_t part_bytes = align_up(static_cast<size_t>(n_clips) * kStatSegs * kStatVals * sizeof(double), 256);
@@ -657,13 +744,14 @@ int enqueue_batch(psla_frontend_t* h, const void* wav, bool pcm16, ClipDesc* des
         sc.attrs = attr;
         sc.numAttrs = overlap_prev_call ? 1 : 0;
         const MetaNone none = {0};
+        const int stats_exact = (h->exact_mean || generic) ? 1 : 0;
         cudaError_t se;
         if (param_meta) {
-            if (pcm16) se = cudaLaunchKernelEx(&sc, clip_stats_kernel<short, true>, static_cast<const short*>(wav), static_cast<const ClipDesc*>(nullptr), h->meta_host, d_part, h->exact_mean);
-            else se = cudaLaunchKernelEx(&sc, clip_stats_kernel<float, true>, static_cast<const float*>(wav), static_cast<const ClipDesc*>(nullptr), h->meta_host, d_part, h->exact_mean);
+            if (pcm16) se = cudaLaunchKernelEx(&sc, clip_stats_kernel<short, true>, static_cast<const short*>(wav), static_cast<const ClipDesc*>(nullptr), h->meta_host, d_part, stats_exact);
+            else se = cudaLaunchKernelEx(&sc, clip_stats_kernel<float, true>, static_cast<const float*>(wav), static_cast<const ClipDesc*>(nullptr), h->meta_host, d_part, stats_exact);
         } else {
-            if (pcm16) se = cudaLaunchKernelEx(&sc, clip_stats_kernel<short, false>, static_cast<const short*>(wav), static_cast<const ClipDesc*>(d_desc), none, d_part, h->exact_mean);
-            else se = cudaLaunchKernelEx(&sc, clip_stats_kernel<float, false>, static_cast<const float*>(wav), static_cast<const ClipDesc*>(d_desc), none, d_part, h->exact_mean);
+            if (pcm16) se = cudaLaunchKernelEx(&sc, clip_stats_kernel<short, false>, static_cast<const short*>(wav), static_cast<const ClipDesc*>(d_desc), none, d_part, stats_exact);
+            else se = cudaLaunchKernelEx(&sc, clip_stats_kernel<float, false>, static_cast<const float*>(wav), static_cast<const ClipDesc*>(d_desc), none, d_part, stats_exact);
         }
         PSLA_CUDA(h, se);
         PSLA_CUDA(h, cudaGetLastError());
@@ -747,9 +835,43 @@ int enqueue_batch(psla_frontend_t* h, const void* wav, bool pcm16, ClipDesc* des
     cfg.attrs = attr;
     cfg.numAttrs = overlap_ok ? 1 : 0;
     const bool trace = h->trace != nullptr;
-    if (trace && h->exact_mean) return PSLA_E_UNSUPPORTED;  // the timeline is compiled for the default clip-mean mode only
-    const cudaError_t le = pcm16 ? launch_stream_kernel<short>(cfg, h->exact_mean, h->mel_spec, param_meta, trace, h->layout, p, h->meta_host)
-                                 : launch_stream_kernel<float>(cfg, h->exact_mean, h->mel_spec, param_meta, trace, h->layout, p, h->meta_host);
+    if (trace && (h->exact_mean || generic)) return PSLA_E_UNSUPPORTED;  // the timeline is compiled for the default clip-mean mode only
+    cudaError_t le;
+    if (generic) {
+        // geometry-generic kernel (generic_kernel.cuh): a plain launch behind the statistics kernel, one CTA per 16 output rows
+        GenericParams gp;
+        gp.wav = wav;
+        gp.desc = d_desc;
+        gp.partials = d_part;
+        gp.window = h->d_gen;
+        gp.tw = reinterpret_cast<const float2*>(h->d_gen + h->gen_off_tw);
+        gp.twn = reinterpret_cast<const float2*>(h->d_gen + h->gen_off_twn);
+        gp.mel_range = reinterpret_cast<const int2*>(h->d_gen + h->gen_off_range);
+        gp.mel_w = h->d_gen + h->gen_off_w;
+        gp.out = out;
+        gp.n_clips = n_clips;
+        gp.T = target_length;
+        gp.nmel = h->nmel;
+        gp.L = h->frame_len;
+        gp.S = h->frame_shift;
+        gp.N = h->nfft;
+        gp.log2M = 0;
+        while ((2 << gp.log2M) < h->nfft) ++gp.log2M;
+        gp.norm_mean = norm_mean;
+        gp.norm_div = norm_div;
+        gp.fill = p.fill;
+        gp.floor_val = p.floor_val;
+        gp.preemph = h->preemph;
+        gp.skip_norm = skip_norm ? 1 : 0;
+        const dim3 ggrid((target_length + kGenFramesPerCta - 1) / kGenFramesPerCta, n_clips);
+        const size_t gsmem = generic_smem_bytes(h->nfft);
+        if (pcm16) fbank_generic_kernel<short><<<ggrid, kGenWarps * 32, gsmem, stream>>>(gp);
+        else fbank_generic_kernel<float><<<ggrid, kGenWarps * 32, gsmem, stream>>>(gp);
+        le = cudaSuccess;
+    } else {
+        le = pcm16 ? launch_stream_kernel<short>(cfg, h->exact_mean, h->mel_spec, param_meta, trace, h->layout, p, h->meta_host)
+                   : launch_stream_kernel<float>(cfg, h->exact_mean, h->mel_spec, param_meta, trace, h->layout, p, h->meta_host);
+    }
     PSLA_CUDA(h, le);
     PSLA_CUDA(h, cudaGetLastError());
     if (slot) {
@@ -776,7 +898,7 @@ int forward_any(psla_frontend_t* h, const void* wav, int64_t wav_samples, bool p
     if (!workspace || workspace_bytes < need || (reinterpret_cast<uintptr_t>(workspace) & 255)) return PSLA_E_WORKSPACE;
     if (!skip_norm && !(norm_div != 0.f)) return PSLA_E_INVALID;
     if (h->layout != PSLA_OUT_TF_F32) {  // frequency-major: a group's 4 frames of a bin are one aligned vector store
-        if (!h->mel_spec || h->nmel != kMaxMel || (target_length % kGroupFrames) != 0 || h->exact_mean || h->trace) return PSLA_E_UNSUPPORTED;
+        if (h->generic() || !h->mel_spec || h->nmel != kMaxMel || (target_length % kGroupFrames) != 0 || h->exact_mean || h->trace) return PSLA_E_UNSUPPORTED;
         if (reinterpret_cast<uintptr_t>(out) & 15) return PSLA_E_INVALID;
     }
     DeviceGuard guard(h->device);
@@ -803,7 +925,7 @@ int forward_any(psla_frontend_t* h, const void* wav, int64_t wav_samples, bool p
         const int a = src1[b];
         if (a < 0 || a >= n_wav) return PSLA_E_INVALID;
         const int64_t n1 = wav_length[a];
-        if (n1 < kFrameLen) return PSLA_E_SHORT_CLIP;  // kaldi.py:142
+        if (n1 < h->frame_len) return PSLA_E_SHORT_CLIP;  // kaldi.py:142
         if (n1 > 0x7fffffff - 8) return PSLA_E_INVALID;
         d.off1 = wav_offset[a];
         d.n1 = static_cast<int>(n1);
@@ -825,7 +947,7 @@ int forward_any(psla_frontend_t* h, const void* wav, int64_t wav_samples, bool p
         }
         d.flags = ((d.off1 & 3) == 0 ? kFlagAligned1 : 0) | ((d.off2 & 3) == 0 ? kFlagAligned2 : 0);
         // whole-clip means are needed in exact mode, and for the zero-padded tail of a shorter mixup partner
-        if (h->exact_mean || (d.n2 > 0 && d.n2 < d.n1)) {
+        if (h->exact_mean || h->generic() || (d.n2 > 0 && d.n2 < d.n1)) {
             d.flags |= kFlagStats;
             any_stats = true;
         }
@@ -845,7 +967,7 @@ int forward_any(psla_frontend_t* h, const void* wav, int64_t wav_samples, bool p
                 d.t1 = m[2] + m[3];
             }
         }
-        const int64_t mfr = frames_of(n1);
+        const int64_t mfr = frames_of(h, n1);
         d.m_eff = static_cast<int>(mfr < target_length ? mfr : target_length);
         // dead groups (4 rows that are all padding / time-masked): [a_lo, a_hi) and [b_lo, G)
         ClipCost& cst = costs[b];
@@ -975,7 +1097,7 @@ int psla_frontend_forward_static(psla_frontend_t* h, const float* wav, int64_t w
                                  int target_length, float norm_mean, float norm_div, int skip_norm, float* out, void* stream) {
     if (!h) return PSLA_E_INVALID;
     if (n_clips > PSLA_STATIC_MAX_CLIPS) return PSLA_E_STATIC_LIMIT;
-    if (!h->param_meta || h->timing) return PSLA_E_STATIC_LIMIT;  // a pinned descriptor slot / timing events would be created
+    if (!h->param_meta || h->timing || h->generic()) return PSLA_E_STATIC_LIMIT;  // a pinned descriptor slot / timing events would be created
     if (h->static_scratch_err != 0 || !h->static_scratch) {
         h->last_cuda = h->static_scratch_err ? h->static_scratch_err : static_cast<int>(cudaErrorInvalidSymbol);
         return PSLA_E_CUDA;

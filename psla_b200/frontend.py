@@ -133,9 +133,14 @@ class GpuFbankFrontend:
                                            25.0, 10.0, 0.97, 20.0, 0.0)
         _lib.check(st, "psla_frontend_create")
         self._h = h
+        fl, fs, nfft, gen = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+        _lib.check(self.lib.psla_frontend_get_geometry(self._h, ctypes.byref(fl), ctypes.byref(fs), ctypes.byref(nfft), ctypes.byref(gen)),
+                   "psla_frontend_get_geometry", self._h)
+        # kaldi.py:138-140: 400 / 160 / 512 at 16 kHz (the fused streaming kernel); other sample rates run the generic kernel
+        self.frame_length, self.frame_shift, self.fft_size, self.generic_path = fl.value, fs.value, nfft.value, bool(gen.value)
         if tables_from == "torch":
-            win = tables.hann_window(400).numpy()
-            mel = tables.mel_banks(self.num_mel_bins, 512, float(self.sample_rate)).numpy()
+            win = tables.hann_window(self.frame_length).numpy()
+            mel = tables.mel_banks(self.num_mel_bins, self.fft_size, float(self.sample_rate)).numpy()
             st = self.lib.psla_frontend_set_tables(self._h, win.ctypes.data, np.ascontiguousarray(mel).ctypes.data)
             _lib.check(st, "psla_frontend_set_tables", self._h)
         elif tables_from != "native":
@@ -168,6 +173,11 @@ class GpuFbankFrontend:
         True: clip means from a statistics kernel, the reference's fp32 expression verbatim."""
         self.exact_clip_mean = bool(enable)
         _lib.check(self.lib.psla_frontend_set_exact_clip_mean(self._h, int(self.exact_clip_mean)), "set_exact_clip_mean", self._h)
+
+    def set_generic_path(self, enable: bool):
+        """Run the 16 kHz geometry through the geometry-generic kernel too (psla_frontend_set_generic_path; tests)."""
+        _lib.check(self.lib.psla_frontend_set_generic_path(self._h, int(bool(enable))), "set_generic_path", self._h)
+        self.generic_path = bool(enable) or (self.frame_length, self.frame_shift, self.fft_size) != (400, 160, 512)
 
     def set_output_layout(self, layout: str = "tf"):
         """Layout of the features the forward calls write (psla_frontend_set_output_layout):
@@ -240,8 +250,8 @@ class GpuFbankFrontend:
         return int(self.lib.psla_frontend_num_frames(self._h, int(n_samples)))
 
     def get_tables(self):
-        win = np.zeros(400, np.float32)
-        mel = np.zeros((self.num_mel_bins, 256), np.float32)
+        win = np.zeros(self.frame_length, np.float32)
+        mel = np.zeros((self.num_mel_bins, self.fft_size // 2), np.float32)
         _lib.check(self.lib.psla_frontend_get_tables(self._h, win.ctypes.data, mel.ctypes.data), "get_tables")
         return win, mel
 

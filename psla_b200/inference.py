@@ -18,20 +18,21 @@ import torch
 
 from .frontend import SAMPLE_RATE, GpuFbankFrontend, PackedWaves
 
-MIN_SAMPLES = 400  # one 25 ms frame: kaldi.fbank asserts on anything shorter (torchaudio/compliance/kaldi.py:142)
+MIN_SAMPLES = 400  # one 25 ms frame at 16 kHz (other rates: frontend.frame_length): kaldi.fbank asserts on anything shorter (torchaudio/compliance/kaldi.py:142)
 
 
-def chunk_offsets(n_samples: int, window: int, hop: Optional[int] = None, keep_tail: bool = True) -> Tuple[np.ndarray, np.ndarray]:
+def chunk_offsets(n_samples: int, window: int, hop: Optional[int] = None, keep_tail: bool = True,
+                  min_samples: int = MIN_SAMPLES) -> Tuple[np.ndarray, np.ndarray]:
     """Start sample and length of every window of a recording of `n_samples`.
 
     Windows start every `hop` samples (default: `window`, i.e. back to back).  The last, shorter window is kept when it
     holds at least one analysis frame (`keep_tail`), like a short file would be; shorter remainders are dropped."""
-    if window < MIN_SAMPLES:
+    if window < min_samples:
         raise ValueError("window must hold at least one 25 ms frame")
     hop = window if hop is None else int(hop)
     if hop < 1:
         raise ValueError("hop must be positive")
-    if n_samples < MIN_SAMPLES:
+    if n_samples < min_samples:
         return np.zeros(0, dtype=np.int64), np.zeros(0, dtype=np.int64)
     starts = np.arange(0, n_samples, hop, dtype=np.int64)
     lengths = np.minimum(window, n_samples - starts)
@@ -39,7 +40,7 @@ def chunk_offsets(n_samples: int, window: int, hop: Optional[int] = None, keep_t
     keep = full.copy()
     if keep_tail and (~full).any():  # the first short window covers the rest of the recording; later ones are inside it
         i = int(np.argmax(~full))
-        keep[i] = lengths[i] >= MIN_SAMPLES
+        keep[i] = lengths[i] >= min_samples
     return starts[keep], lengths[keep]
 
 
@@ -80,8 +81,9 @@ class LongRecordingFrontend:
     """
 
     def __init__(self, frontend: GpuFbankFrontend, wave: torch.Tensor, window_s: float = 10.0, hop_s: Optional[float] = None,
-                 sample_rate: int = SAMPLE_RATE, keep_tail: bool = True):
+                 sample_rate: Optional[int] = None, keep_tail: bool = True):
         self.frontend = frontend
+        sample_rate = int(frontend.sample_rate if sample_rate is None else sample_rate)
         w = wave.detach()
         w = w[0] if w.dim() == 2 else w  # channel 0, as kaldi.fbank selects it (kaldi.py:136)
         if w.dtype not in (torch.float32, torch.int16):
@@ -96,7 +98,7 @@ class LongRecordingFrontend:
         self.n_samples = n
         window = int(round(window_s * sample_rate))
         hop = None if hop_s is None else int(round(hop_s * sample_rate))
-        self.starts, self.lengths = chunk_offsets(n, window, hop, keep_tail)
+        self.starts, self.lengths = chunk_offsets(n, window, hop, keep_tail, min_samples=frontend.frame_length)
 
     def __len__(self) -> int:
         return len(self.starts)
@@ -150,7 +152,8 @@ class LongRecordingFrontend:
         per_window = torch.cat(outs, dim=0) if outs else torch.zeros(0, device=dev)
         clip = None
         if aggregate is not None and len(outs):
-            frames = np.minimum(np.maximum(1 + (self.lengths - 400) // 160, 0), self.frontend.target_length)
+            fl, fs = self.frontend.frame_length, self.frontend.frame_shift
+            frames = np.minimum(np.maximum(1 + (self.lengths - fl) // fs, 0), self.frontend.target_length)
             w = torch.as_tensor(frames, dtype=per_window.dtype, device=per_window.device)
             clip = AGGREGATES[aggregate](per_window, w)
         return RecordingPrediction(self.starts.copy(), per_window, clip, aggregate)

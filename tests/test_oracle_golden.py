@@ -100,6 +100,28 @@ def test_getitem_restatement(golden_dir, name, use_torchaudio):
     assert k == len(g["feats"])
 
 
+@pytest.mark.parametrize("use_torchaudio", [True, False], ids=["torchaudio", "restated"])
+def test_getitem_restatement_at_other_sample_rates(golden_dir, use_torchaudio):
+    """The unmodified reference with `torchaudio.load` reporting 8 ... 48 kHz: kaldi.fbank derives the frame geometry from the
+    rate (kaldi.py:138-140); the oracle must follow (pins the generic-geometry kernel)."""
+    g = _load(golden_dir, "getitem_rates.npz")
+    conf = json.loads(str(g["conf"]))
+    waves = tiny_dataset_waves()
+    fill = ((torch.zeros(1) - conf["mean"]) / conf["std"]).numpy()[0]
+    for sr in g["rates"]:
+        sr = int(sr)
+        shift, size, padded = O.frame_geometry(sr)
+        assert (shift, size) == (int(sr * 0.010), int(sr * 0.025)) and padded >= size and padded & (padded - 1) == 0
+        random.seed(sr)
+        np.random.seed(sr)
+        torch.manual_seed(sr)
+        for i in range(len(waves)):
+            out, _ = O.item_torch(waves, i, conf, random, np.random, use_torchaudio=use_torchaudio, sample_rate=sr)
+            ref = g[f"feats_{sr}"][i]
+            assert np.array_equal(ref == fill, out.numpy() == fill), (sr, i)
+            assert np.abs(out.numpy() - ref).max() <= HOST_DRIFT, (sr, i)
+
+
 def test_batch_oracle_equals_item_oracle():
     waves = tiny_dataset_waves()
     out = O.batch_torch(waves, [0, 5, 2], [-1, 1, 4], [0.0, 0.4, 0.6], [(0, 0, 0, 0), (3, 5, 10, 7), (100, 20, 90, 6)],

@@ -3,7 +3,7 @@
 // int(sr * 0.010), padded_window_size = next power of two) -- 8 kHz (200 / 80 / 256) ... 48 kHz (1200 / 480 / 2048).
 // "generalising the kernel beyond 16 kHz".  Every recipe of the reference resamples to 16 kHz
 // (egs/fsd50k/prep_fsd.py:17-35), so this path is built for correctness and coverage, not for the roofline: one warp per
-// frame, a radix-2 FFT in shared memory, the clip means always taken from clip_stats_kernel (the reference's expression
+// frame, a radix-4 Stockham FFT in shared memory, the clip means always taken from clip_stats_kernel (the reference's expression
 // verbatim, audioset_dataset.py:92,98-99,116-117).  The 16 kHz geometry keeps the specialised streaming kernel;
 // psla_frontend_set_generic_path(handle, 1) runs it through this kernel too (a second, independent implementation the tests
 // compare the streaming kernel with).
@@ -23,7 +23,7 @@ struct GenericParams {
     const ClipDesc* desc;     // [n_clips] (device memory: this path never uses parameter-space descriptors)
     const double* partials;   // clip_stats_kernel's sums, exact mode (every clip carries kFlagStats)
     const float* window;      // [L] analysis window
-    const float2* tw;         // [M/2]      exp(-2 pi i j / M),  M = N / 2
+    const float2* tw;         // [M]        exp(-2 pi i j / M),  M = N / 2
     const float2* twn;        // [M/2 + 1]  exp(-2 pi i k / N)
     const int2* mel_range;    // [nmel] (first, one-past-last) spectrum bin with non-zero weight
     const float* mel_w;       // [nmel][M] dense weights (kaldi.py:436-511)
@@ -130,10 +130,9 @@ __global__ void __launch_bounds__(kGenWarps * 32) fbank_generic_kernel(const Gen
         for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
         const float mu = sum / static_cast<float>(p.L);  // per-frame DC removal, kaldi.py:183-186
         __syncwarp();
-        // ---- pre-emphasis with replicate padding (:193-198), window (:200), zero padding to N (:204-206); written as the
-        //      M complex points z[c] = (y[2c], y[2c+1]) in bit-reversed order for the in-place DIT below ----
+        // ---- pre-emphasis with replicate padding (:193-198), window (:200), zero padding to N (:204-206); stored as the M
+        //      complex points z[c] = (y[2c], y[2c+1]) in natural order ----
         float* Zf = reinterpret_cast<float*>(Z);
-        const int shift = 32 - p.log2M;
         for (int j = lane; j < p.N; j += 32) {
             float y = 0.f;
             if (j < p.L) {
@@ -141,29 +140,61 @@ __global__ void __launch_bounds__(kGenWarps * 32) fbank_generic_kernel(const Gen
                 const float sp = stage[j > 0 ? j - 1 : 0] - mu;
                 y = (s - p.preemph * sp) * __ldg(p.window + j);
             }
-            const unsigned r = __brev(static_cast<unsigned>(j >> 1)) >> shift;
-            Zf[2 * r + (j & 1)] = y;
+            Zf[j] = y;
         }
         __syncwarp();
-        // ---- M-point complex FFT, radix-2 decimation in time, in place ----
-        for (int s = 0; s < p.log2M; ++s) {
-            const int half = 1 << s;
-            for (int q = lane; q < (M >> 1); q += 32) {
-                const int jj = q & (half - 1);
-                const int pos = ((q >> s) << (s + 1)) + jj;
-                const float2 w = __ldg(p.tw + (jj << (p.log2M - 1 - s)));
-                const float2 a = Z[pos], c = Z[pos + half];
-                const float vr = c.x * w.x - c.y * w.y, vi = c.x * w.y + c.y * w.x;
-                Z[pos] = make_float2(a.x + vr, a.y + vi);
-                Z[pos + half] = make_float2(a.x - vr, a.y - vi);
+        // ---- M-point complex FFT: Stockham autosort (no bit reversal; every pass reads one buffer with unit stride and
+        //      writes the other), radix-4 passes and one radix-2 pass when log2(M) is odd.  Pass with Ns points already
+        //      combined, radix R:  v[r] = in[j + r M/R] * W_(Ns R)^(r k),  k = j mod Ns;  out[(j - k) R + k + r Ns] = DFT_R(v)[r]
+        float2* src = Z;
+        float2* dst = reinterpret_cast<float2*>(stage);  // the staged samples are dead
+        int Ns = 1;
+        for (; Ns * 4 <= M; Ns *= 4) {
+            const int q4 = M >> 2, tstep = M / (4 * Ns);
+#pragma unroll 2
+            for (int j = lane; j < q4; j += 32) {
+                const int k = j & (Ns - 1);
+                const float2 a0 = src[j];
+                float2 a1 = src[j + q4], a2 = src[j + 2 * q4], a3 = src[j + 3 * q4];
+                if (Ns > 1) {
+                    const float2 w1 = __ldg(p.tw + k * tstep), w2 = __ldg(p.tw + 2 * k * tstep), w3 = __ldg(p.tw + 3 * k * tstep);
+                    a1 = make_float2(a1.x * w1.x - a1.y * w1.y, a1.x * w1.y + a1.y * w1.x);
+                    a2 = make_float2(a2.x * w2.x - a2.y * w2.y, a2.x * w2.y + a2.y * w2.x);
+                    a3 = make_float2(a3.x * w3.x - a3.y * w3.y, a3.x * w3.y + a3.y * w3.x);
+                }
+                const float2 t0 = make_float2(a0.x + a2.x, a0.y + a2.y), t1 = make_float2(a0.x - a2.x, a0.y - a2.y);
+                const float2 t2 = make_float2(a1.x + a3.x, a1.y + a3.y);
+                const float2 t3 = make_float2(a1.y - a3.y, -(a1.x - a3.x));  // -i (a1 - a3)
+                const int j0 = ((j - k) << 2) + k;
+                dst[j0] = make_float2(t0.x + t2.x, t0.y + t2.y);
+                dst[j0 + Ns] = make_float2(t1.x + t3.x, t1.y + t3.y);
+                dst[j0 + 2 * Ns] = make_float2(t0.x - t2.x, t0.y - t2.y);
+                dst[j0 + 3 * Ns] = make_float2(t1.x - t3.x, t1.y - t3.y);
             }
             __syncwarp();
+            float2* t = src;
+            src = dst;
+            dst = t;
         }
-        // ---- spectrum of the real frame from the packed transform, power (:616-618) ----
+        if (Ns < M) {  // Ns == M / 2: the last radix-2 pass, k = j
+            const int q2 = M >> 1;
+            for (int j = lane; j < q2; j += 32) {
+                const float2 w = __ldg(p.tw + j);
+                const float2 a = src[j], c = src[j + q2];
+                const float vr = c.x * w.x - c.y * w.y, vi = c.x * w.y + c.y * w.x;
+                dst[j] = make_float2(a.x + vr, a.y + vi);
+                dst[j + q2] = make_float2(a.x - vr, a.y - vi);
+            }
+            __syncwarp();
+            float2* t = src;
+            src = dst;
+            dst = t;
+        }
+        // ---- spectrum of the real frame from the packed transform (now in `src`), power (:616-618), into the other buffer ----
         //   E = (Z[k] + conj(Z[M-k])) / 2,  O = (Z[k] - conj(Z[M-k])) / 2i,  X[k] = E + W_N^k O,  X[M-k] = conj(E - W_N^k O)
-        float* P = stage;  // the staged samples are dead
+        float* P = reinterpret_cast<float*>(dst);
         for (int k = lane; k <= (M >> 1); k += 32) {
-            const float2 a = Z[k], zb = Z[(M - k) & (M - 1)];
+            const float2 a = src[k], zb = src[(M - k) & (M - 1)];
             const float er = 0.5f * (a.x + zb.x), ei = 0.5f * (a.y - zb.y);
             const float orr = 0.5f * (a.y + zb.y), oi = -0.5f * (a.x - zb.x);
             const float2 w = __ldg(p.twn + k);
@@ -188,7 +219,7 @@ __global__ void __launch_bounds__(kGenWarps * 32) fbank_generic_kernel(const Gen
             }
             __stcs(row + m, v);
         }
-        __syncwarp();  // P (= stage) is rewritten by the next frame
+        __syncwarp();  // both buffers are rewritten by the next frame
     }
 }
 

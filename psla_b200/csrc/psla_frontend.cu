@@ -297,14 +297,14 @@ cudaError_t prepare_all(size_t smem) {
 int upload_generic_tables(psla_frontend* h) {
     const int L = h->frame_len, N = h->nfft, M = N / 2, nmel = h->nmel;
     const size_t off_tw = align_up(static_cast<size_t>(L), 4);
-    const size_t off_twn = off_tw + static_cast<size_t>(M);             // M/2 complex
+    const size_t off_twn = off_tw + 2 * static_cast<size_t>(M);         // M complex
     const size_t off_range = off_twn + align_up(static_cast<size_t>(M) + 2, 4);  // M/2 + 1 complex
     const size_t off_w = off_range + align_up(2 * static_cast<size_t>(nmel), 4);
     const size_t total = off_w + static_cast<size_t>(nmel) * M;
     std::vector<float> buf(total, 0.f);
     std::memcpy(buf.data(), h->window.data(), sizeof(float) * L);
     const double two_pi = 6.283185307179586476925286766559;
-    for (int j = 0; j < M / 2; ++j) {
+    for (int j = 0; j < M; ++j) {
         buf[off_tw + 2 * j] = static_cast<float>(std::cos(two_pi * j / M));
         buf[off_tw + 2 * j + 1] = static_cast<float>(-std::sin(two_pi * j / M));
     }

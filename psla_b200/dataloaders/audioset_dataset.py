@@ -218,7 +218,7 @@ class RawItem:
     params: P.ItemParams
     labels: torch.Tensor  # [label_num] float32 (multi-hot, or mixup-soft)
     noise: Optional[torch.Tensor] = None  # [T, F] U[0,1) field of the noise augmentation when it is drawn on the host
-    conf: Optional[tuple] = None  # (num_mel_bins, target_length, mean, std, skip_norm) of the dataset that made it
+    conf: Optional[tuple] = None  # (num_mel_bins, target_length, mean, std, skip_norm, sample_rate) of the dataset that made it
 
 
 @dataclass
@@ -232,7 +232,7 @@ class RawBatch:
     noise_scale: Optional[np.ndarray] = None  # [B] float64, set when the noise / roll augmentation is on
     roll: Optional[np.ndarray] = None  # [B] int32
     noise: Optional[torch.Tensor] = None  # [B, T, F] host-drawn fields (pinned), or None: the kernel draws them
-    conf: Optional[tuple] = None  # (num_mel_bins, target_length, mean, std, skip_norm)
+    conf: Optional[tuple] = None  # (num_mel_bins, target_length, mean, std, skip_norm, sample_rate)
     slot: int = -1  # PinnedSlotPool slot holding the waveforms (waves.wav is then resolved by the FrontendLoader)
     labels_shape: Optional[tuple] = None  # set when the labels sit in the slot as well (`labels` is then None in transit)
 
@@ -268,8 +268,9 @@ def _default_frontend_loader(conf) -> "FrontendLoader":
         raise RuntimeError("this RawBatch carries no frontend configuration; wrap the loader in FrontendLoader(loader, frontend)")
     key = (torch.cuda.current_device(), conf)
     if key not in _DEFAULT_LOADERS:
-        nmel, T, mean, std, skip = conf
-        fe = GpuFbankFrontend({"num_mel_bins": nmel, "target_length": T, "mean": mean, "std": std, "skip_norm": skip})
+        nmel, T, mean, std, skip, *rest = conf
+        fe = GpuFbankFrontend({"num_mel_bins": nmel, "target_length": T, "mean": mean, "std": std, "skip_norm": skip},
+                              sample_rate=rest[0] if rest else 16000)
         _DEFAULT_LOADERS[key] = FrontendLoader(None, fe)
     return _DEFAULT_LOADERS[key]
 
@@ -304,12 +305,23 @@ class AudiosetDataset(Dataset):
         self.label_num = len(self.index_dict)
         say("number of classes is {:d}".format(self.label_num))
         self.loader = loader or default_loader
+        sr = self.audio_conf.get("sample_rate")  # optional extra key; otherwise the rate of the first file that is loaded
+        self.sample_rate = int(sr) if sr is not None else None
 
     def __len__(self):
         return len(self.data)
 
     def _load(self, path) -> torch.Tensor:
-        wav, _sr = self.loader(path)
+        # The reference hands the decoder's rate to kaldi.fbank PER FILE (:91,119), which derives the frame geometry from it
+        # (kaldi.py:138-140).  A GPU frontend handle has one geometry, so a dataset must be of one rate (every recipe
+        # resamples to 16 kHz, egs/*/prep_*.py); the rate travels with the batch and a second rate is an error here.
+        wav, sr = self.loader(path)
+        if sr is not None:
+            if self.sample_rate is None:
+                self.sample_rate = int(sr)
+            elif int(sr) != self.sample_rate:
+                raise ValueError(f"{path}: sample rate {int(sr)} differs from the dataset's {self.sample_rate}; "
+                                 "one frontend handles one frame geometry (resample, or use one dataset per rate)")
         return wav
 
     def __getitem__(self, index) -> RawItem:
@@ -340,7 +352,8 @@ class AudiosetDataset(Dataset):
         return RawItem(w1, w2, params, torch.FloatTensor(label_indices), field, self._conf_key())
 
     def _conf_key(self) -> tuple:
-        return (self.melbins, self.audio_conf.get("target_length"), self.norm_mean, self.norm_std, bool(self.skip_norm))
+        return (self.melbins, self.audio_conf.get("target_length"), self.norm_mean, self.norm_std, bool(self.skip_norm),
+                self.sample_rate if self.sample_rate is not None else 16000)
 
     def features(self, index: int, frontend: Optional[GpuFbankFrontend] = None) -> Tuple[torch.Tensor, torch.Tensor]:
         """Per-item compatibility with the reference's `dataset[index] -> (fbank [T, F], label_indices)` (:202-205) for code
@@ -569,6 +582,8 @@ class FrontendLoader:
     def features(self, batch: RawBatch, with_labels: bool = False):
         """fbank [B, T, F] on the device (and the labels on the device when `with_labels`), asynchronous on the current stream."""
         self._reap()
+        if batch.conf is not None and len(batch.conf) > 5 and int(batch.conf[5]) != self.frontend.sample_rate:
+            raise ValueError(f"the batch's files are {int(batch.conf[5])} Hz, the frontend was built for {self.frontend.sample_rate} Hz")
         waves, labels_dev, j = self._stage(batch, with_labels)
         fbank = self.frontend.forward_packed(waves, batch.src1, batch.src2, batch.lam, batch.masks)
         if j is not None:

@@ -60,7 +60,7 @@ def test_stock_dataloader_without_collate_fn_yields_raw_batches(files, golden_di
     for batch in dl:
         assert isinstance(batch, RawBatch) and batch.slot == -1
         assert batch.waves.wav.dtype == torch.int16 and (workers == 0 and torch.cuda.is_available() or not batch.waves.wav.is_pinned())
-        assert batch.conf == (128, 256, -4.6476, 4.5699, False)
+        assert batch.conf == (128, 256, -4.6476, 4.5699, False, 16000)  # the files' rate travels with the batch
         B = len(batch)
         assert np.array_equal(batch.labels.numpy(), g["eval_labels"][seen:seen + B])
         assert (batch.src2 == -1).all() and batch.masks.shape == (B, 4) and not batch.masks.any()
@@ -70,6 +70,21 @@ def test_stock_dataloader_without_collate_fn_yields_raw_batches(files, golden_di
             assert o % 4 == 0 and torch.equal(batch.waves.wav[o:o + n], to_pcm16(waves[(seen + b) % 8]).reshape(-1))
         seen += B
     assert seen == len(ds) == 16
+
+
+def test_one_sample_rate_per_dataset(files, golden_dir):
+    """The reference derives the frame geometry per file from the decoder's rate (audioset_dataset.py:91,119); a frontend
+    handle has one geometry: the rate travels in the batch's configuration and a second rate in one dataset is an error."""
+    g, conf = _conf(golden_dir, "eval")
+    waves = tiny_dataset_waves()
+    odd = json.load(open(files[0]))["data"][3]["wav"]
+    ds = AudiosetDataset(files[0], conf, label_csv=files[1], verbose=False, loader=lambda p: (waves[0].clone(), 44100 if p == odd else 32000))
+    assert ds[0].conf[5] == 32000 and ds[1].conf[5] == 32000 and ds.sample_rate == 32000
+    with pytest.raises(ValueError, match="sample rate 44100"):
+        ds[3]
+    ds2 = AudiosetDataset(files[0], dict(conf, sample_rate=16000), label_csv=files[1], verbose=False, loader=lambda p: (waves[0].clone(), 8000))
+    with pytest.raises(ValueError, match="sample rate 8000"):
+        ds2[0]
 
 
 def test_pooled_collate_packs_into_shared_slots(files, golden_dir):

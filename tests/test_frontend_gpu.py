@@ -557,6 +557,52 @@ def test_overlapping_launches_keep_stream_order(FE):
             assert all(torch.equal(g_, w_) for g_, w_ in zip(got, want)), (mode, rep)
 
 
+def test_overlap_fuzz_random_batches(FE):
+    """Random batches (1..128 clips, ragged lengths, mixup with shorter / longer partners, masks, three target lengths) back
+    to back in PSLA_OVERLAP_STREAM mode into output ranges carved from ONE arena (so consecutive ranges sometimes overlap
+    and the library has to fall back to a plain launch), each result cloned by a consumer right behind the call:
+    bit-identical to the same calls with overlap off.  Part of the substitute for compute-sanitizer (profiles/r02a/sanitizer.md)."""
+    from psla_b200.frontend import pack_waveforms
+    fe = FE({"num_mel_bins": 128, "target_length": 256, "mean": MEAN, "std": STD})
+    dev = fe.device
+    rng = np.random.default_rng(2024)
+    pool = [synth_wave(4000 + i, int(rng.integers(400, 48000)), ("gauss", "am", "int16")[i % 3]) for i in range(40)]
+    pk = pack_waveforms(pool, device=dev)
+    calls = []
+    for _ in range(48):
+        B = int(rng.choice([1, 2, 3, 7, 24, 60, 128]))
+        T = int(rng.choice([64, 256, 301]))
+        s1 = rng.integers(0, 40, B).astype(np.int32)
+        s2 = np.where(rng.random(B) < 0.5, rng.integers(0, 40, B), -1).astype(np.int32)
+        lam = rng.beta(10, 10, B)
+        masks = np.zeros((B, 4), np.int32)
+        for b in range(B):
+            if rng.random() < 0.5:
+                masks[b] = (int(rng.integers(0, 100)), int(rng.integers(0, 28)), int(rng.integers(0, T - 40)), int(rng.integers(0, 40)))
+        calls.append((B, T, s1, s2, lam, masks))
+    arena = torch.empty(3 * 128 * 301 * 128, device=dev)
+    starts = [int(rng.integers(0, 2 * 128 * 301 * 128 // 4)) * 4 for _ in calls]  # 16-byte aligned, anywhere in the first two thirds
+
+    def run():
+        got = []
+        for (B, T, s1, s2, lam, masks), st in zip(calls, starts):
+            out = arena[st:st + B * T * 128].view(B, T, 128)
+            fe.forward_packed(pk, s1, s2, lam, masks, out=out, target_length=T)
+            got.append(out.clone())
+        torch.cuda.synchronize()
+        return got
+
+    fe.set_launch_overlap("off")
+    want = run()
+    for mode in ("stream", "call"):
+        fe.set_launch_overlap(mode)
+        for rep in range(3):
+            got = run()
+            for i, (g_, w_) in enumerate(zip(got, want)):
+                assert torch.equal(g_, w_), (mode, rep, i, calls[i][0], calls[i][1])
+    fe.close()
+
+
 def test_c2_audioset_train_batch(fe):
     """C2: 100 clips, 150 waveforms, every even clip mixed, masks drawn like the reference (48 / 192)."""
     B = 100
